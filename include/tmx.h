@@ -1,0 +1,156 @@
+/*
+ * tmx.h -- C ABI of the B200-native TriangleMix prefill path (libtmx.so).
+ *
+ * The reference (ackerm0n/vllm-trianglemix) has no native ABI for this path: it is
+ * 1.1k lines of eager PyTorch.  Each entry point below therefore cites the Python
+ * function whose work it replaces (paths relative to the reference root).  The
+ * Python host (vllm_trianglemix_b200/) keeps the reference's class and method
+ * signatures and calls these through ctypes with raw device pointers.
+ *
+ * Conventions
+ *   - every pointer is a DEVICE pointer unless its name ends in _host;
+ *   - the caller owns all buffers (outputs and workspace); the library allocates
+ *     nothing persistent except per-process cached TMA descriptors / attributes;
+ *   - every call only ENQUEUES work on `stream` (a cudaStream_t) -- no host sync;
+ *   - return value 0 = TMX_OK, otherwise a tmx_status (see tmx_strerror);
+ *   - mask parameters: si = num_sink_tokens, sl = sliding_window_size,
+ *     last = num_last_tokens  (vllm/attention/trianglemix_attention.py:14-36);
+ *   - element predicate for query row i, key column j of a length-N sequence
+ *       triangle: j <= i && (j <= si || i - j <= sl || N - i < last)
+ *       dense   : j <= i
+ *     which is bit-exact with the reference's loops (:82-89, :126-129, :192-196).
+ */
+#ifndef TMX_H_
+#define TMX_H_
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+typedef struct CUstream_st* tmx_stream_t; /* == cudaStream_t */
+
+typedef enum {
+  TMX_OK = 0,
+  TMX_ERR_BAD_ARG = 1,      /* null pointer, negative size, unknown enum        */
+  TMX_ERR_BAD_SHAPE = 2,    /* head_dim != 128, Hq % Hkv != 0, ...              */
+  TMX_ERR_ALIGNMENT = 3,    /* pointer / stride not 16-byte aligned             */
+  TMX_ERR_WORKSPACE = 4,    /* workspace null or smaller than tmx_attn_workspace_bytes */
+  TMX_ERR_ARCH = 5,         /* device is not compute capability 10.x            */
+  TMX_ERR_CUDA = 6,         /* a CUDA runtime/driver call failed (see tmx_last_cuda_error) */
+  TMX_ERR_UNSUPPORTED = 7   /* valid request this build cannot serve            */
+} tmx_status;
+
+/* mask_mode of a layer: the output of should_use_triangle()
+ * (vllm/attention/trianglemix_attention.py:263-278). */
+enum { TMX_MODE_DENSE_CAUSAL = 0, TMX_MODE_TRIANGLE = 1,
+       /* no mask at all (bidirectional): what the reference op computes when neither the
+        * helper nor the caller supplies a mask (vllm/attention/ascend_trianglemix.py:96-97,
+        * e.g. every seq_len <= 2048).  Attention only; not a mask-generator mode. */
+       TMX_MODE_NONE = 2 };
+
+/* the five 0/1 pieces the generator exposes (:53, :93, :133, :173, :200) */
+enum { TMX_PIECE_STREAMING = 0, TMX_PIECE_LAST = 1, TMX_PIECE_MIDDLE = 2,
+       TMX_PIECE_TRIANGLE = 3, TMX_PIECE_DENSE = 4 };
+
+/* element types of the compat (N x N) mask outputs */
+enum { TMX_F32 = 0, TMX_BF16 = 1, TMX_F16 = 2 };
+
+/* which attention kernel serves tmx_prefill_attn */
+enum { TMX_KERNEL_AUTO = 0,   /* tcgen05 kernel where it applies, else mma.sync */
+       TMX_KERNEL_MMA = 1,    /* warp-level mma.sync kernel (also the on-GPU cross-check) */
+       TMX_KERNEL_TCGEN05 = 2 /* tcgen05/TMEM/TMA kernel */ };
+
+const char* tmx_strerror(int status);
+const char* tmx_last_cuda_error(void);
+int tmx_version(void);
+
+/* ---- masks -------------------------------------------------------------- */
+
+/* Packed bitmask of one piece.  Row i occupies row_stride_words uint32 words;
+ * bit b (LSB first) of word w = piece[i, 32*w + b]; bits at columns >= N and
+ * padding words are 0.  row_stride_words must be a multiple of 4 (16-byte rows)
+ * and >= ceil(N/32).  Replaces the O(N^2) Python loops
+ * _create_{streaming,last,middle,triangle,dense}_mask
+ * (vllm/attention/trianglemix_attention.py:53-219) for native consumers. */
+int tmx_mask_bits(uint32_t* out, int64_t row_stride_words, int N, int si, int sl,
+                  int last, int piece, tmx_stream_t stream);
+
+/* The same pieces as a dense N x N tensor of 0/1 in `dtype` with leading
+ * dimension ld (elements) -- the exact return value of the reference's
+ * _create_*_mask methods (:53-219). */
+int tmx_mask_dense01(void* out, int dtype, int64_t ld, int N, int si, int sl,
+                     int last, int piece, tmx_stream_t stream);
+
+/* Additive form {0, -inf} of the triangle / dense-causal mask in `dtype`:
+ * get_attention_mask's return value (:221-261, the torch.where at :254-258). */
+int tmx_mask_additive(void* out, int dtype, int64_t ld, int N, int si, int sl,
+                      int last, int mode, tmx_stream_t stream);
+
+/* `-inf -> fill` rewrite of an additive mask, in place or out of place:
+ * AscendNPUTriangleMixOptimizer.optimize_mask_for_npu
+ * (vllm/attention/ascend_trianglemix.py:114-141). numel elements of `dtype`. */
+int tmx_mask_rewrite_neg_inf(void* out, const void* in, int dtype, int64_t numel,
+                             float fill, tmx_stream_t stream);
+
+/* Arbitrary additive N x N mask (values 0 / -inf, as a caller may pass in
+ * `attn_mask`, vllm/attention/ascend_trianglemix.py:57,84,97) -> packed bitmask
+ * (warp ballot).  *bad_count (device int32, may be null) receives the number of
+ * elements that are neither 0 nor -inf. */
+int tmx_mask_bits_from_additive(uint32_t* out, int64_t row_stride_words,
+                                const void* in, int dtype, int64_t ld, int N,
+                                int32_t* bad_count, tmx_stream_t stream);
+
+/* ---- block index ---------------------------------------------------------
+ * Per (sequence, query tile of block_m rows) the KV tiles (block_n columns) the
+ * mask touches, as at most two half-open tile ranges, plus the tile classes.
+ * ranges[t*4 + {0,1,2,3}] = lo0, hi0, lo1, hi1 (hi exclusive; empty range lo==hi);
+ * counts[t] = number of touched KV tiles; full[t*2+{0,1}] = number of leading
+ * tiles of range0 / range1 that are FULL (no per-element predicate needed) --
+ * remaining touched tiles are PARTIAL, everything else is SKIPPED.
+ * Query tile slot of (sequence b, tile q) = cu_seqlens[b] / block_m + b + q;
+ * n_slots = total_T / block_m + B slots must be provided; unused slots get
+ * empty ranges.  cu_seqlens: int32 [B+1] on the device. */
+int tmx_block_index(int32_t* ranges, int32_t* counts, int32_t* full,
+                    const int32_t* cu_seqlens, int B, int total_T, int block_m,
+                    int block_n, int si, int sl, int last, int mode,
+                    tmx_stream_t stream);
+
+/* ---- masked GQA prefill attention ------------------------------------------
+ * out[t, h, :] = softmax_j( q[t,h,:] . k[j, h / (Hq/Hkv), :] * scale + mask[t,j] ) v[j, ...]
+ * over the keys j of t's own sequence, i.e. AscendTriangleMixAttention.forward
+ * (vllm/attention/ascend_trianglemix.py:86-106) with the additive mask of
+ * get_attention_mask folded into tile skipping + an in-register predicate, in the
+ * varlen layout of vLLM's AttentionImpl.forward
+ * (vllm/attention/backends/abstract.py:158-171; q [T,Hq,D], k/v [T,Hkv,D]).
+ * bf16 in, bf16 out, fp32 accumulation.  D must be 128.
+ * strides are in elements between consecutive tokens; heads are contiguous
+ * (stride D).  cu_seqlens: int32 [B+1] device.  lse (optional): float [Hq, total_T],
+ * natural-log-sum-exp of the scaled masked scores.
+ * bitmask (optional): packed [max_seqlen, stride] mask in tmx_mask_bits layout,
+ * indexed by the row/column INSIDE each sequence (every sequence shares it, as the
+ * reference broadcasts one (S,S) mask over the batch).  When given, every touched
+ * tile reads mask bits instead of evaluating the predicate; `mode` then only
+ * selects which tiles are touched (TMX_MODE_NONE = all).  Used for caller-supplied
+ * masks and as a cross-check of the analytic path. */
+size_t tmx_attn_workspace_bytes(int B, int total_T, int max_seqlen, int Hq, int Hkv,
+                                int D, int si, int sl, int last, int mode, int kernel);
+
+int tmx_prefill_attn(void* out, const void* q, const void* k, const void* v,
+                     const int32_t* cu_seqlens, int B, int total_T, int max_seqlen,
+                     int Hq, int Hkv, int D, int64_t q_stride_t, int64_t kv_stride_t,
+                     int64_t o_stride_t, float scale, int si, int sl, int last,
+                     int mode, const uint32_t* bitmask, int64_t bitmask_stride_words,
+                     float* lse, void* workspace, size_t workspace_bytes, int kernel,
+                     tmx_stream_t stream);
+
+/* Number of kernels the last tmx_prefill_attn call on this thread enqueued
+ * (bench.py's gpu_launches accounting). */
+int tmx_last_launch_count(void);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* TMX_H_ */

@@ -156,7 +156,7 @@ def additive(mask01: np.ndarray, dtype=np.float32) -> np.ndarray:
 def rewrite_neg_inf(mask: np.ndarray, value: float = -1e6) -> np.ndarray:
     if mask.size == 0:
         return mask
-    return np.where(np.isinf(mask), np.asarray(value, dtype=mask.dtype), mask)
+    return np.where(np.isinf(mask) & (mask < 0), np.asarray(value, dtype=mask.dtype), mask)
 
 
 # --------------------------------------------------------------------------

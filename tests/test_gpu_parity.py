@@ -1,0 +1,257 @@
+"""GPU parity tests: the CUDA path (through the C ABI) against the CPU oracle and the
+golden vectors produced by the unmodified reference.  Masks: bit-exact.  Attention:
+bf16 kernel vs the fp32 oracle on the same bf16-rounded inputs, atol 1.5e-2 / rtol 1e-2
+(the reference repo's own bar for bf16 attention kernels, tests/kernels/attention/
+test_flash_attn.py:179,192)."""
+import hashlib
+import json
+import os
+
+import numpy as np
+import pytest
+import torch
+
+from oracle import trianglemix_oracle as orc
+
+pytestmark = pytest.mark.gpu
+ATOL, RTOL = 1.5e-2, 1e-2
+GOLDEN = os.path.join(os.path.dirname(__file__), "golden")
+with open(os.path.join(GOLDEN, "masks.json")) as f:
+    G = json.load(f)
+ATTN = np.load(os.path.join(GOLDEN, "attn_small.npz"))
+KERNELS = ["mma"]
+
+
+@pytest.fixture(scope="module")
+def tmx():
+    import vllm_trianglemix_b200 as m
+    return m
+
+
+@pytest.fixture(scope="module")
+def ops():
+    from vllm_trianglemix_b200 import ops as o
+    return o
+
+
+DEV = "cuda:0"
+
+
+def _u32(t):
+    return t.cpu().numpy().view(np.uint32)
+
+
+# ------------------------------------------------------------------ masks
+@pytest.mark.parametrize("case", G["cases"], ids=lambda c: "N%d_%d_%d_%d" % (c["N"], c["si"], c["sl"], c["num_last"]))
+def test_mask_bits_golden(ops, case):
+    n, si, sl, last = case["N"], case["si"], case["sl"], case["num_last"]
+    words = (n + 31) // 32
+    for piece in orc.PIECES:
+        bits = _u32(ops.mask_bits(n, si, sl, last, piece, DEV))
+        assert not bits[:, words:].any()
+        got = np.ascontiguousarray(bits[:, :words])
+        assert hashlib.sha256(got.tobytes()).hexdigest() == case[piece + "_sha"], piece
+        assert int(np.unpackbits(got.view(np.uint8)).sum()) == case[piece]
+
+
+@pytest.mark.parametrize("case", G["big"], ids=lambda c: "N%d" % c["N"])
+def test_mask_bits_golden_big(ops, case):
+    n, si, sl, last = case["N"], case["si"], case["sl"], case["num_last"]
+    bits = _u32(ops.mask_bits(n, si, sl, last, "triangle", DEV))[:, :(n + 31) // 32]
+    assert hashlib.sha256(np.ascontiguousarray(bits).tobytes()).hexdigest() == case["triangle_sha"]
+
+
+@pytest.mark.parametrize("dtype", [torch.float32, torch.bfloat16, torch.float16])
+@pytest.mark.parametrize("n,si,sl,last", [(300, 4, 32, 64), (97, 4, 32, 64), (130, 0, 0, 1), (1, 4, 32, 64),
+                                          (2, 0, 0, 0), (64, 7, 3, 200), (64, 100, 3, 5), (1000, 4, 32, 64)])
+def test_generator_api_matches_oracle(tmx, dtype, n, si, sl, last):
+    gen = tmx.TriangleMixMaskGenerator(tmx.TriangleMixConfig(si, sl, last))
+    dev = torch.device(DEV)
+    for piece in orc.PIECES:
+        m = getattr(gen, "_create_%s_mask" % piece)(n, dev, dtype)
+        assert m.dtype == dtype and tuple(m.shape) == (n, n)
+        assert np.array_equal(m.float().cpu().numpy(), orc.piece_closed(piece, n, si, sl, last).astype(np.float32))
+    for tri, mode in ((True, orc.TRIANGLE), (False, orc.DENSE_CAUSAL)):
+        a = gen.get_attention_mask(n, 3, dev, dtype, use_triangle=tri)
+        assert a.dtype == dtype
+        assert np.array_equal(a.float().cpu().numpy(), orc.additive(orc.mask_closed(n, si, sl, last, mode)))
+        assert gen.get_attention_mask(n, 3, dev, dtype, use_triangle=tri) is a        # cached object
+        assert (n, 3, str(dev), str(dtype), tri) in gen._mask_cache
+    gen.clear_cache()
+    assert not gen._mask_cache
+
+
+@pytest.mark.parametrize("n", [32768, 131072])
+def test_mask_bits_long_by_row_chunks(ops, n):
+    si, sl, last = 4, 32, 64
+    bits = ops.mask_bits(n, si, sl, last, "triangle", DEV)
+    stride = bits.shape[1]
+    total = int(torch.ops.aten.sum(_popcount(bits)).item())
+    assert total == orc.attended_pairs(n, si, sl, last, orc.TRIANGLE)
+    for r0 in (0, 64, n // 2 - 7, n - last - 70, n - 256):
+        r1 = min(n, r0 + 256)
+        want = orc.pack_bits(orc.mask_closed(n, si, sl, last, orc.TRIANGLE, r0, r1), stride)
+        assert np.array_equal(_u32(bits[r0:r1]), want)
+
+
+def _popcount(x):
+    x = x.to(torch.int64) & 0xFFFFFFFF
+    x = x - ((x >> 1) & 0x55555555)
+    x = (x & 0x33333333) + ((x >> 2) & 0x33333333)
+    x = (x + (x >> 4)) & 0x0F0F0F0F
+    return ((x * 0x01010101) & 0xFFFFFFFF) >> 24
+
+
+def test_bits_from_additive_and_rewrite(tmx, ops):
+    n, si, sl, last = 777, 3, 17, 40
+    dev = torch.device(DEV)
+    for dtype in (torch.float32, torch.bfloat16, torch.float16):
+        add = ops.mask_additive(n, si, sl, last, ops.TRIANGLE, dev, dtype)
+        bits, bad = ops.bits_from_additive(add)
+        assert int(bad.item()) == 0
+        assert torch.equal(bits, ops.mask_bits(n, si, sl, last, "triangle", dev))
+        rew = tmx.AscendNPUTriangleMixOptimizer.optimize_mask_for_npu(add)
+        assert not torch.isinf(rew).any()
+        want = orc.rewrite_neg_inf(orc.additive(orc.mask_closed(n, si, sl, last, orc.TRIANGLE)))
+        assert np.array_equal(rew.float().cpu().numpy(), want.astype(np.float32) if dtype == torch.float32
+                              else torch.from_numpy(want).to(dtype).float().numpy())
+    add = ops.mask_additive(64, si, sl, last, ops.TRIANGLE, dev, torch.float32)
+    add[5, 3] = -2.5
+    _, bad = ops.bits_from_additive(add)
+    assert int(bad.item()) == 1
+
+
+@pytest.mark.parametrize("bm,bn", [(64, 64), (128, 64), (128, 128), (32, 32)])
+def test_block_index_vs_bruteforce(ops, bm, bn):
+    lens = [1, 63, 64, 65, 300, 1000, 2049]
+    cu = np.concatenate([[0], np.cumsum(lens)]).astype(np.int32)
+    total = int(cu[-1])
+    for (si, sl, last) in ((4, 32, 64), (0, 0, 1), (7, 3, 200), (100, 3, 5), (1, 70, 130)):
+        for mode in (orc.TRIANGLE, orc.DENSE_CAUSAL):
+            ranges, counts, full = ops.block_index(torch.from_numpy(cu).to(DEV), total, bm, bn, si, sl, last, mode)
+            ranges, counts, full = ranges.cpu().numpy(), counts.cpu().numpy(), full.cpu().numpy()
+            used = set()
+            for b, n in enumerate(lens):
+                m = orc.mask_closed(n, si, sl, last, mode)
+                for q in range((n + bm - 1) // bm):
+                    slot = cu[b] // bm + b + q
+                    used.add(slot)
+                    rows = m[q * bm:(q + 1) * bm]
+                    touched = [j for j in range((n + bn - 1) // bn) if rows[:, j * bn:(j + 1) * bn].any()]
+                    lo0, hi0, lo1, hi1 = ranges[slot]
+                    listed = list(range(lo0, hi0)) + list(range(lo1, hi1))
+                    assert set(touched) <= set(listed)
+                    if not (lo1 == hi1 and mode == orc.TRIANGLE):
+                        assert listed == touched            # exact when two ranges / dense
+                    assert counts[slot] == len(listed)
+                    nfull = sum(1 for j in listed if rows[:, j * bn:(j + 1) * bn].all()
+                                and (j + 1) * bn <= n and rows.shape[0] > 0)
+                    assert full[slot].sum() <= nfull       # FULL is sufficient, never over-claimed
+            for slot in range(total // bm + len(lens)):
+                if slot not in used:
+                    assert counts[slot] == 0
+
+
+# ------------------------------------------------------------------ attention
+def _bf16(a):
+    return torch.from_numpy(a.copy()).view(torch.bfloat16)
+
+
+def _check(out, ref, what):
+    rep = orc.error_report(out, ref, ATOL, RTOL)
+    assert rep["violations"] == 0, (what, rep)
+    return rep
+
+
+@pytest.mark.parametrize("kernel", KERNELS)
+@pytest.mark.parametrize("tag", ["a", "b", "c"])
+def test_attention_golden(ops, tag, kernel):
+    s, hq, hkv, d, si, sl, last = [int(x) for x in ATTN[tag + "_params"]]
+    q, k, v = _bf16(ATTN[tag + "_q"])[0], _bf16(ATTN[tag + "_k"])[0], _bf16(ATTN[tag + "_v"])[0]
+    cu = torch.tensor([0, s], dtype=torch.int32, device=DEV)
+    for name, mode in (("tri", ops.TRIANGLE), ("dense", ops.DENSE_CAUSAL)):
+        out = ops.prefill_attn(q.to(DEV), k.to(DEV), v.to(DEV), cu, s, d ** -0.5, si, sl, last, mode, kernel=kernel)
+        _check(out.cpu(), torch.from_numpy(ATTN["%s_%s_out" % (tag, name)])[0], (tag, name, kernel))
+    if tag == "a":
+        out = ops.prefill_attn(q.to(DEV), k.to(DEV), v.to(DEV), cu, s, d ** -0.5, 0, 0, 0, ops.NONE, kernel=kernel)
+        _check(out.cpu(), torch.from_numpy(ATTN["a_nomask_out"])[0], (tag, "nomask", kernel))
+
+
+def _rand(t, hq, hkv, d=128, seed=0, qscale=1.0):
+    g = torch.Generator().manual_seed(seed)
+    q = (torch.randn(t, hq, d, generator=g) * qscale).bfloat16()
+    k = torch.randn(t, hkv, d, generator=g).bfloat16()
+    v = torch.randn(t, hkv, d, generator=g).bfloat16()
+    return q, k, v
+
+
+@pytest.mark.parametrize("kernel", KERNELS)
+@pytest.mark.parametrize("mode", [0, 1])
+@pytest.mark.parametrize("n,hq,hkv,si,sl,last", [
+    (2048, 16, 8, 4, 32, 64),          # BASELINE config 1
+    (1, 4, 4, 4, 32, 64), (2, 2, 1, 0, 0, 0), (63, 2, 2, 4, 32, 64), (65, 4, 1, 4, 32, 64),
+    (129, 8, 2, 0, 0, 1), (1000, 4, 2, 7, 3, 200), (513, 2, 1, 100, 3, 5), (3000, 4, 2, 1, 70, 130),
+    (4500, 2, 1, 4, 32, 64),           # long enough for split-KV of the dense tail rows
+])
+def test_attention_vs_oracle(ops, n, hq, hkv, si, sl, last, mode, kernel):
+    q, k, v = _rand(n, hq, hkv, seed=n)
+    cu = torch.tensor([0, n], dtype=torch.int32, device=DEV)
+    scale = 128 ** -0.5
+    out, lse = ops.prefill_attn(q.to(DEV), k.to(DEV), v.to(DEV), cu, n, scale, si, sl, last, mode,
+                                return_lse=True, kernel=kernel)
+    ref = orc.attention_varlen_fp32(q, k, v, [0, n], scale, si, sl, last, mode)
+    _check(out.cpu(), ref, (n, mode, kernel))
+    # lse against the oracle's scores on a few rows
+    rows = sorted(set([0, n // 2, n - 1]))
+    m = torch.from_numpy(orc.additive(orc.mask_closed(n, si, sl, last, mode)))[rows]
+    kk = k.float().repeat_interleave(hq // hkv, dim=1)
+    sc = torch.einsum("rhd,jhd->hrj", q[rows].float(), kk) * scale + m
+    assert torch.allclose(lse.cpu()[:, rows], torch.logsumexp(sc, dim=-1), atol=2e-2, rtol=1e-3)
+
+
+@pytest.mark.parametrize("kernel", KERNELS)
+def test_attention_bitmask_source_identical(ops, kernel):
+    n, hq, hkv, si, sl, last = 1500, 4, 2, 4, 32, 64
+    q, k, v = _rand(n, hq, hkv, seed=3)
+    cu = torch.tensor([0, n], dtype=torch.int32, device=DEV)
+    for mode, piece in ((ops.TRIANGLE, "triangle"), (ops.DENSE_CAUSAL, "dense")):
+        a = ops.prefill_attn(q.to(DEV), k.to(DEV), v.to(DEV), cu, n, 0.088, si, sl, last, mode, kernel=kernel)
+        bits = ops.mask_bits(n, si, sl, last, piece, DEV)
+        b = ops.prefill_attn(q.to(DEV), k.to(DEV), v.to(DEV), cu, n, 0.088, si, sl, last, mode, bitmask=bits,
+                             kernel=kernel)
+        assert torch.equal(a, b)
+        c = ops.prefill_attn(q.to(DEV), k.to(DEV), v.to(DEV), cu, n, 0.088, 0, 0, 0, ops.NONE, bitmask=bits,
+                             kernel=kernel)
+        _check(c.cpu().float(), a.cpu().float(), "all-tiles bitmask")
+
+
+@pytest.mark.parametrize("kernel", KERNELS)
+@pytest.mark.parametrize("mode", [0, 1])
+def test_attention_varlen(ops, mode, kernel):
+    lens = [700, 1, 64, 4500, 129, 2048]
+    t = sum(lens)
+    hq, hkv, si, sl, last = 8, 2, 4, 32, 64
+    q, k, v = _rand(t, hq, hkv, seed=11)
+    cu_list = [0]
+    for n in lens:
+        cu_list.append(cu_list[-1] + n)
+    cu = torch.tensor(cu_list, dtype=torch.int32, device=DEV)
+    # strided inputs: q/k/v are slices of a fused qkv buffer, as vLLM's qkv_proj output is
+    fused = torch.cat([q.reshape(t, -1), k.reshape(t, -1), v.reshape(t, -1)], dim=1).to(DEV)
+    qd = fused[:, :hq * 128].view(t, hq, 128)
+    kd = fused[:, hq * 128:(hq + hkv) * 128].view(t, hkv, 128)
+    vd = fused[:, (hq + hkv) * 128:].view(t, hkv, 128)
+    out = ops.prefill_attn(qd, kd, vd, cu, max(lens), 128 ** -0.5, si, sl, last, mode, kernel=kernel)
+    ref = orc.attention_varlen_fp32(q, k, v, cu_list, 128 ** -0.5, si, sl, last, mode)
+    _check(out.cpu(), ref, ("varlen", mode, kernel))
+
+
+@pytest.mark.parametrize("kernel", KERNELS)
+def test_attention_peaky_softmax(ops, kernel):
+    n, hq, hkv = 1024, 4, 1
+    q, k, v = _rand(n, hq, hkv, seed=5, qscale=4.0)
+    cu = torch.tensor([0, n], dtype=torch.int32, device=DEV)
+    for mode in (0, 1):
+        out = ops.prefill_attn(q.to(DEV), k.to(DEV), v.to(DEV), cu, n, 128 ** -0.5, 4, 32, 64, mode, kernel=kernel)
+        ref = orc.attention_varlen_fp32(q, k, v, [0, n], 128 ** -0.5, 4, 32, 64, mode)
+        _check(out.cpu(), ref, ("peaky", mode, kernel))

@@ -1,0 +1,198 @@
+"""vLLM-shaped attention backend for the TriangleMix prefill path.
+
+Keeps the signatures of the reference's plug-in slot so that
+``Attention(..., attn_backend=TriangleMixBackend, **extra_impl_args)``
+(vllm/attention/layer.py:102,186-201) can install it the way
+ChunkedLocalAttention / EncoderOnlyAttention install theirs:
+
+* ``AttentionBackend`` statics          vllm/attention/backends/abstract.py:27-83
+* ``AttentionImpl.__init__/forward``    vllm/attention/backends/abstract.py:142-171
+* metadata fields                       vllm/v1/attention/backends/flash_attn.py:110-140
+* in-place ``output`` contract          vllm/v1/attention/backends/flash_attn.py:449-458,549
+
+The classes are duck-typed (no ``import vllm``: the vllm wheel in this image is an
+unrelated upstream release).  Prefill only: K/V of the call are the whole
+context, as in ``_forward_encoder_attention`` (flash_attn.py:578-633); ``kv_cache``
+is ignored.  TriangleMix parameters and ``layer_idx`` travel as extra impl kwargs,
+the way ``dual_chunk_attention_config`` + ``layer_idx`` do in the reference's
+vllm/model_executor/models/qwen3.py:150-153.
+"""
+from __future__ import annotations
+
+from dataclasses import dataclass
+from typing import List, Optional, Tuple, Type
+
+import torch
+
+from . import ops
+from ._lib import TmxError
+from .trianglemix_attention import TriangleMixAttention, TriangleMixConfig
+
+
+@dataclass
+class TriangleMixMetadata:
+    """Subset of FlashAttentionMetadata this path reads (flash_attn.py:110-140)."""
+    num_actual_tokens: int
+    max_query_len: int
+    query_start_loc: torch.Tensor          # int32 [B+1] on the device
+    max_seq_len: int
+    seq_lens: Optional[torch.Tensor] = None
+    causal: bool = True
+    query_start_loc_cpu: Optional[torch.Tensor] = None
+
+
+class TriangleMixMetadataBuilder:
+    """Builds TriangleMixMetadata from the fields of CommonAttentionMetadata
+    (vllm/v1/attention/backends/utils.py:45-84)."""
+
+    def __init__(self, kv_cache_spec=None, layer_names=None, vllm_config=None, device=None):
+        self.device = device
+
+    def build(self, common_prefix_len: int = 0, common_attn_metadata=None, fast_build: bool = False):
+        m = common_attn_metadata
+        return TriangleMixMetadata(
+            num_actual_tokens=int(m.num_actual_tokens), max_query_len=int(m.max_query_len),
+            query_start_loc=m.query_start_loc, max_seq_len=int(getattr(m, "max_seq_len", m.max_query_len)),
+            seq_lens=getattr(m, "seq_lens", None), causal=getattr(m, "causal", True),
+            query_start_loc_cpu=getattr(m, "query_start_loc_cpu", None))
+
+    @staticmethod
+    def from_seq_lens(seq_lens: List[int], device) -> TriangleMixMetadata:
+        """Convenience for tests / benchmarks: prefill of len(seq_lens) whole sequences."""
+        cu = [0]
+        for n in seq_lens:
+            cu.append(cu[-1] + int(n))
+        cu_cpu = torch.tensor(cu, dtype=torch.int32)
+        return TriangleMixMetadata(
+            num_actual_tokens=cu[-1], max_query_len=max(seq_lens) if seq_lens else 0,
+            query_start_loc=cu_cpu.to(device), max_seq_len=max(seq_lens) if seq_lens else 0,
+            seq_lens=torch.tensor(list(seq_lens), dtype=torch.int32, device=device),
+            causal=True, query_start_loc_cpu=cu_cpu)
+
+
+class TriangleMixImpl:
+    """AttentionImpl for TriangleMix prefill (signature: abstract.py:142-171)."""
+
+    def __init__(
+        self,
+        num_heads: int,
+        head_size: int,
+        scale: float,
+        num_kv_heads: Optional[int] = None,
+        alibi_slopes: Optional[List[float]] = None,
+        sliding_window: Optional[int] = None,
+        kv_cache_dtype: str = "auto",
+        logits_soft_cap: Optional[float] = None,
+        attn_type: str = "decoder",
+        kv_sharing_target_layer_name: Optional[str] = None,
+        # ---- extra_impl_args (layer.py:186-201) ----
+        trianglemix_config: Optional[TriangleMixConfig] = None,
+        layer_idx: Optional[int] = None,
+        num_layers: Optional[int] = None,
+        kernel: str = "auto",
+    ) -> None:
+        if alibi_slopes is not None or logits_soft_cap:
+            raise NotImplementedError("TriangleMixImpl supports neither ALiBi nor logits soft-capping")
+        if sliding_window is not None:
+            raise NotImplementedError("model-level sliding_window is not combined with TriangleMix; "
+                                      "set TriangleMixConfig.sliding_window_size instead")
+        if attn_type != "decoder":
+            raise NotImplementedError("TriangleMixImpl is decoder self-attention only")
+        if kv_sharing_target_layer_name is not None:
+            raise NotImplementedError("KV sharing is not supported")
+        self.num_heads = num_heads
+        self.head_size = head_size
+        self.scale = float(scale)
+        self.num_kv_heads = num_heads if num_kv_heads is None else num_kv_heads
+        self.num_queries_per_kv = self.num_heads // self.num_kv_heads
+        self.kv_cache_dtype = kv_cache_dtype
+        self.layer_idx = layer_idx or 0            # reference ascend_trianglemix.py:43
+        self.kernel = kernel
+        self.trianglemix_attn = None
+        if trianglemix_config is not None and num_layers is not None:
+            self.trianglemix_attn = TriangleMixAttention(trianglemix_config, num_layers)
+
+    def mask_mode(self) -> Tuple[int, int, int, int]:
+        """(mode, si, sl, last): the per-layer dense-vs-triangle switch
+        (reference trianglemix_attention.py:263-278) feeding the kernel's mask_mode.
+        Without a helper the layer is plain causal attention (what the stock backend
+        the inert hook falls through to computes, reference qwen3.py:185-189)."""
+        if self.trianglemix_attn is None:
+            return (ops.DENSE_CAUSAL, 0, 0, 0)
+        si, sl, last = self.trianglemix_attn.config.mask_params()
+        return (self.trianglemix_attn.mask_mode(self.layer_idx), si, sl, last)
+
+    def forward(
+        self,
+        layer,
+        query: torch.Tensor,
+        key: torch.Tensor,
+        value: torch.Tensor,
+        kv_cache: Optional[torch.Tensor],
+        attn_metadata: Optional[TriangleMixMetadata],
+        output: Optional[torch.Tensor] = None,
+        output_scale: Optional[torch.Tensor] = None,
+        output_block_scale: Optional[torch.Tensor] = None,
+    ) -> torch.Tensor:
+        assert output is not None, "Output tensor must be provided."           # flash_attn.py:449
+        if output_scale is not None or output_block_scale is not None:        # flash_attn.py:451-454
+            raise NotImplementedError("fused output quantization is not supported for TriangleMixImpl")
+        if attn_metadata is None:                                              # profiling run, :456-458
+            return output
+        if not attn_metadata.causal:
+            raise NotImplementedError("TriangleMixImpl is causal prefill only")
+        t = attn_metadata.num_actual_tokens
+        q = query[:t].view(t, self.num_heads, self.head_size)
+        k = key[:t].view(t, self.num_kv_heads, self.head_size)
+        v = value[:t].view(t, self.num_kv_heads, self.head_size)
+        out = output[:t].view(t, self.num_heads, self.head_size)
+        mode, si, sl, last = self.mask_mode()
+        ops.prefill_attn(q, k, v, attn_metadata.query_start_loc, attn_metadata.max_query_len, self.scale,
+                         si, sl, last, mode, out=out, kernel=self.kernel)
+        return output
+
+
+class TriangleMixBackend:
+    """AttentionBackend statics (abstract.py:27-83; FlashAttention's values flash_attn.py:37-88)."""
+
+    accept_output_buffer: bool = True
+    supports_quant_query_input: bool = False
+
+    @staticmethod
+    def get_name() -> str:
+        return "TRIANGLEMIX_B200"
+
+    @staticmethod
+    def get_impl_cls() -> Type[TriangleMixImpl]:
+        return TriangleMixImpl
+
+    @staticmethod
+    def get_metadata_cls() -> Type[TriangleMixMetadata]:
+        return TriangleMixMetadata
+
+    @classmethod
+    def make_metadata(cls, *args, **kwargs) -> TriangleMixMetadata:
+        return cls.get_metadata_cls()(*args, **kwargs)
+
+    @staticmethod
+    def get_builder_cls() -> Type[TriangleMixMetadataBuilder]:
+        return TriangleMixMetadataBuilder
+
+    @staticmethod
+    def get_kv_cache_shape(num_blocks: int, block_size: int, num_kv_heads: int, head_size: int,
+                           cache_dtype_str: str = "auto") -> Tuple[int, ...]:
+        if block_size % 16 != 0:
+            raise ValueError("Block size must be a multiple of 16.")
+        return (2, num_blocks, block_size, num_kv_heads, head_size)
+
+    @staticmethod
+    def get_supported_head_sizes() -> List[int]:
+        return [128]
+
+    @staticmethod
+    def get_supported_dtypes() -> List[torch.dtype]:
+        return [torch.bfloat16]
+
+    @classmethod
+    def full_cls_name(cls) -> Tuple[str, str]:
+        return (cls.__module__, cls.__qualname__)

@@ -1,0 +1,160 @@
+// C-ABI entry points that are not kernels themselves: error strings, launch
+// accounting, workspace sizing and the tmx_prefill_attn dispatcher.
+#include <mutex>
+#include <string>
+#include "tmx_attn.cuh"
+
+namespace tmx {
+
+static thread_local int g_launches = 0;
+static std::mutex g_err_mu;
+static std::string g_cuda_err;
+
+void count_launch(int n) { g_launches += n; }
+void reset_launch_count() { g_launches = 0; }
+
+void set_cuda_error(cudaError_t e, const char* where) {
+  std::lock_guard<std::mutex> lk(g_err_mu);
+  g_cuda_err = std::string(cudaGetErrorName(e)) + ": " + cudaGetErrorString(e) + " at " + where;
+}
+
+int device_sm_count() {
+  static int sms = 0;
+  if (sms == 0) {
+    int dev = 0;
+    cudaGetDevice(&dev);
+    cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
+    if (sms <= 0) sms = 148;
+  }
+  return sms;
+}
+
+int check_arch() {
+  static int status = -1;
+  if (status < 0) {
+    int dev = 0, major = 0;
+    if (cudaGetDevice(&dev) != cudaSuccess ||
+        cudaDeviceGetAttribute(&major, cudaDevAttrComputeCapabilityMajor, dev) != cudaSuccess) {
+      set_cuda_error(cudaGetLastError(), "cudaDeviceGetAttribute");
+      return TMX_ERR_CUDA;
+    }
+    status = (major == 10) ? TMX_OK : TMX_ERR_ARCH;
+  }
+  return status;
+}
+
+namespace {
+size_t align_up(size_t x, size_t a) { return (x + a - 1) / a * a; }
+
+struct Plan {
+  int kernel;      // TMX_KERNEL_MMA / TMX_KERNEL_TCGEN05
+  int bm, bn;
+  int n_slots, last_tiles, nsplit_max;
+  size_t off_slots, off_part_o, off_part_ml, total;
+};
+
+Plan make_plan(int B, int total_T, int max_seqlen, int Hq, int last, int mode, int kernel) {
+  Plan pl{};
+  pl.kernel = (kernel == TMX_KERNEL_AUTO) ? TMX_KERNEL_MMA : kernel;
+  pl.bn = 64;
+  pl.bm = (mode == TMX_MODE_TRIANGLE) ? 64 : 128;
+  if (pl.kernel == TMX_KERNEL_TCGEN05) { pl.bm = 128; pl.bn = 128; }
+  pl.n_slots = total_T / pl.bm + B;
+  pl.last_tiles = 0; pl.nsplit_max = 0;
+  if (pl.kernel == TMX_KERNEL_MMA && mode == TMX_MODE_TRIANGLE) {
+    int ns = nsplit_max(max_seqlen, pl.bn);
+    int lt = last_tiles_max(last, pl.bm);
+    if (lt > 0 && ceil_div(max_seqlen, pl.bn) >= kSplitMinTiles) { pl.last_tiles = lt; pl.nsplit_max = ns; }
+  }
+  size_t off = 0;
+  pl.off_slots = off; off = align_up(off + sizeof(SlotInfo) * (size_t)pl.n_slots, 256);
+  size_t parts = (size_t)B * pl.last_tiles * pl.nsplit_max * Hq;
+  pl.off_part_o = off; off = align_up(off + parts * pl.bm * 128 * sizeof(float), 256);
+  pl.off_part_ml = off; off = align_up(off + parts * pl.bm * sizeof(float2), 256);
+  pl.total = off;
+  return pl;
+}
+}  // namespace
+}  // namespace tmx
+
+using namespace tmx;
+
+extern "C" const char* tmx_strerror(int status) {
+  switch (status) {
+    case TMX_OK: return "ok";
+    case TMX_ERR_BAD_ARG: return "bad argument (null pointer, negative size or unknown enum)";
+    case TMX_ERR_BAD_SHAPE: return "unsupported shape (head_dim must be 128, Hq % Hkv == 0, strides >= H*D)";
+    case TMX_ERR_ALIGNMENT: return "pointer or stride not 16-byte aligned";
+    case TMX_ERR_WORKSPACE: return "workspace missing or smaller than tmx_attn_workspace_bytes()";
+    case TMX_ERR_ARCH: return "device is not compute capability 10.x (B200, sm_100a)";
+    case TMX_ERR_CUDA: return "CUDA call failed (see tmx_last_cuda_error)";
+    case TMX_ERR_UNSUPPORTED: return "request not supported by this build";
+    default: return "unknown status";
+  }
+}
+
+extern "C" const char* tmx_last_cuda_error(void) {
+  static thread_local std::string copy;
+  std::lock_guard<std::mutex> lk(g_err_mu);
+  copy = g_cuda_err;
+  return copy.c_str();
+}
+
+extern "C" int tmx_version(void) { return 100; }
+extern "C" int tmx_last_launch_count(void) { return g_launches; }
+
+extern "C" size_t tmx_attn_workspace_bytes(int B, int total_T, int max_seqlen, int Hq, int Hkv,
+                                           int D, int si, int sl, int last, int mode, int kernel) {
+  (void)Hkv; (void)D; (void)si; (void)sl;
+  if (B <= 0 || total_T <= 0) return 256;
+  return make_plan(B, total_T, max_seqlen, Hq, last, mode, kernel).total;
+}
+
+extern "C" int tmx_prefill_attn(void* out, const void* q, const void* k, const void* v,
+                                const int32_t* cu_seqlens, int B, int total_T, int max_seqlen,
+                                int Hq, int Hkv, int D, int64_t q_stride_t, int64_t kv_stride_t,
+                                int64_t o_stride_t, float scale, int si, int sl, int last,
+                                int mode, const uint32_t* bitmask, int64_t bitmask_stride_words,
+                                float* lse, void* workspace, size_t workspace_bytes, int kernel,
+                                tmx_stream_t stream) {
+  reset_launch_count();
+  if (B < 0 || total_T < 0 || max_seqlen < 0 || Hq <= 0 || Hkv <= 0) return TMX_ERR_BAD_ARG;
+  if (mode < TMX_MODE_DENSE_CAUSAL || mode > TMX_MODE_NONE) return TMX_ERR_BAD_ARG;
+  if (kernel < TMX_KERNEL_AUTO || kernel > TMX_KERNEL_TCGEN05) return TMX_ERR_BAD_ARG;
+  if (D != 128 || Hq % Hkv != 0) return TMX_ERR_BAD_SHAPE;
+  if (q_stride_t < (int64_t)Hq * D || kv_stride_t < (int64_t)Hkv * D || o_stride_t < (int64_t)Hq * D)
+    return TMX_ERR_BAD_SHAPE;
+  if (B == 0 || total_T == 0) return TMX_OK;
+  if (!out || !q || !k || !v || !cu_seqlens) return TMX_ERR_BAD_ARG;
+  if (max_seqlen <= 0 || max_seqlen > total_T) return TMX_ERR_BAD_ARG;
+  auto mis = [](const void* p) { return (reinterpret_cast<uintptr_t>(p) & 15u) != 0; };
+  if (mis(out) || mis(q) || mis(k) || mis(v) || (q_stride_t % 8) || (kv_stride_t % 8) || (o_stride_t % 8))
+    return TMX_ERR_ALIGNMENT;
+  if (bitmask && (bitmask_stride_words * 32 < max_seqlen || bitmask_stride_words % 2)) return TMX_ERR_BAD_SHAPE;
+  int st = check_arch();
+  if (st != TMX_OK) return st;
+
+  Plan pl = make_plan(B, total_T, max_seqlen, Hq, last, mode, kernel);
+  if (!workspace || workspace_bytes < pl.total || mis(workspace)) return TMX_ERR_WORKSPACE;
+  cudaStream_t s = (cudaStream_t)stream;
+  uint8_t* ws = static_cast<uint8_t*>(workspace);
+
+  AttnParams p{};
+  p.q = (const __nv_bfloat16*)q; p.k = (const __nv_bfloat16*)k; p.v = (const __nv_bfloat16*)v;
+  p.out = (__nv_bfloat16*)out; p.lse = lse; p.cu = cu_seqlens;
+  p.slots = reinterpret_cast<SlotInfo*>(ws + pl.off_slots);
+  p.bitmask = bitmask; p.bitmask_stride = bitmask_stride_words;
+  p.part_o = reinterpret_cast<float*>(ws + pl.off_part_o);
+  p.part_ml = reinterpret_cast<float2*>(ws + pl.off_part_ml);
+  p.q_stride = q_stride_t; p.kv_stride = kv_stride_t; p.o_stride = o_stride_t;
+  p.B = B; p.total_T = total_T; p.max_seqlen = max_seqlen; p.Hq = Hq; p.Hkv = Hkv;
+  p.n_slots = pl.n_slots; p.last_tiles = pl.last_tiles; p.nsplit_max = pl.nsplit_max;
+  p.si = si; p.sl = sl; p.last = last; p.mode = mode;
+  p.scale_log2 = scale * 1.4426950408889634f;
+
+  st = build_slots(reinterpret_cast<SlotInfo*>(ws + pl.off_slots), pl.n_slots, cu_seqlens, B,
+                   max_seqlen, pl.bm, pl.bn, si, sl, last, mode, s);
+  if (st != TMX_OK) return st;
+  if (pl.kernel == TMX_KERNEL_TCGEN05) return launch_attn_sm100(p, s);
+  return launch_attn_mma(p, pl.bm, s);
+}

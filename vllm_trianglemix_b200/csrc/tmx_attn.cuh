@@ -1,0 +1,31 @@
+// Parameters shared by the attention kernels and their launchers.
+#pragma once
+#include "tmx_sched.cuh"
+
+namespace tmx {
+
+struct AttnParams {
+  const __nv_bfloat16* q;
+  const __nv_bfloat16* k;
+  const __nv_bfloat16* v;
+  __nv_bfloat16* out;
+  float* lse;                 // [Hq, total_T] or null
+  const int* cu;              // [B + 1]
+  const SlotInfo* slots;      // [n_slots]
+  const uint32_t* bitmask;    // optional packed mask (B == 1)
+  long long bitmask_stride;   // words per row
+  float* part_o;              // split-KV partials
+  float2* part_ml;
+  long long q_stride, kv_stride, o_stride;   // elements per token
+  int B, total_T, max_seqlen, Hq, Hkv;
+  int n_slots, last_tiles, nsplit_max;
+  int si, sl, last, mode;
+  float scale_log2;           // scale * log2(e)
+};
+
+int build_slots(SlotInfo* slots, int n_slots, const int* cu, int B, int max_seqlen, int bm, int bn,
+                int si, int sl, int last, int mode, cudaStream_t s);
+int launch_attn_mma(const AttnParams& p, int bm, cudaStream_t s);
+int launch_attn_sm100(const AttnParams& p, cudaStream_t s);
+
+}  // namespace tmx

@@ -1,0 +1,131 @@
+// Shared device helpers of libtmx: mask predicates in closed form, tile
+// classification, error plumbing.  Predicates follow the reference's loops
+// (vllm/attention/trianglemix_attention.py:82-89,126-129,166-169,192-196,218).
+#pragma once
+#include <cuda_runtime.h>
+#include <cuda_bf16.h>
+#include <cuda_fp16.h>
+#include <stdint.h>
+#include "tmx.h"
+
+namespace tmx {
+
+struct MaskParams {
+  int si, sl, last, mode;  // mode: TMX_MODE_*
+};
+
+// First query row that attends every earlier key: N - i < last  <=>  i >= N - last + 1.
+__host__ __device__ __forceinline__ int first_dense_row(int n, int last) {
+  long long r = (long long)n - (long long)last + 1;
+  return r < 0 ? 0 : (r > n ? n : (int)r);
+}
+
+// Triangle / dense predicate for one element (i, j) of a length-n sequence.
+__host__ __device__ __forceinline__ bool attends(int i, int j, int n, int lrow,
+                                                 int si, int sl, int mode) {
+  if (mode == TMX_MODE_NONE) return j < n;
+  if (j > i) return false;
+  if (mode == TMX_MODE_DENSE_CAUSAL) return true;
+  return (j <= si) | (i - j <= sl) | (i >= lrow);
+}
+
+// One of the five pieces.
+__host__ __device__ __forceinline__ bool piece_at(int piece, int i, int j, int n,
+                                                  int lrow, int si, int sl) {
+  if (j > i) return false;
+  bool stream = (j <= si) | (i - j <= sl);
+  bool tail = i >= lrow;
+  switch (piece) {
+    case TMX_PIECE_STREAMING: return stream;
+    case TMX_PIECE_LAST: return !stream & tail;
+    case TMX_PIECE_MIDDLE: return !stream & !tail;
+    case TMX_PIECE_TRIANGLE: return stream | tail;
+    default: return true;
+  }
+}
+
+// Bits [lo, hi] (inclusive, clipped to 0..31) of a 32-bit word.
+__host__ __device__ __forceinline__ uint32_t bit_span(long long lo, long long hi) {
+  if (lo < 0) lo = 0;
+  if (hi > 31) hi = 31;
+  if (hi < lo) return 0u;
+  uint32_t upto_hi = (hi == 31) ? 0xffffffffu : ((1u << (hi + 1)) - 1u);
+  return upto_hi & ~((1u << lo) - 1u);
+}
+
+// 32 columns [c0, c0+32) of row i of a piece, as a word (LSB = column c0).
+// Closed form: each row's attended set is a union of at most two intervals.
+__host__ __device__ __forceinline__ uint32_t piece_word(int piece, int i, long long c0,
+                                                        int n, int lrow, int si, int sl) {
+  long long ii = i;
+  uint32_t causal = bit_span(0 - c0, ii - c0);
+  if (piece == TMX_PIECE_DENSE) return causal;
+  long long sink_hi = (si < ii ? (long long)si : ii);
+  uint32_t stream = bit_span(0 - c0, sink_hi - c0) | bit_span(ii - sl - c0, ii - c0);
+  stream &= causal;
+  bool tail = i >= lrow;
+  switch (piece) {
+    case TMX_PIECE_STREAMING: return stream;
+    case TMX_PIECE_LAST: return tail ? (causal & ~stream) : 0u;
+    case TMX_PIECE_MIDDLE: return tail ? 0u : (causal & ~stream);
+    default: return tail ? causal : stream;  // TRIANGLE
+  }
+}
+
+// ---- tile level (block index) ---------------------------------------------
+// Touched KV tiles of a query tile with rows [r0, r1] (inclusive, r1 < n):
+// at most two half-open tile ranges [lo0,hi0) U [lo1,hi1), disjoint, ascending.
+struct TileRanges {
+  int lo0, hi0, lo1, hi1;
+};
+
+__host__ __device__ __forceinline__ TileRanges touched_tiles(int r0, int r1, int n, int bn,
+                                                             int lrow, int si, int sl, int mode) {
+  TileRanges t;
+  if (mode == TMX_MODE_NONE) {
+    t.lo0 = 0; t.hi0 = (n - 1) / bn + 1; t.lo1 = t.hi1 = 0;
+    return t;
+  }
+  int diag = r1 / bn;  // last tile holding a column <= r1
+  if (mode == TMX_MODE_DENSE_CAUSAL || r1 >= lrow) {
+    t.lo0 = 0; t.hi0 = diag + 1; t.lo1 = t.hi1 = 0;
+    return t;
+  }
+  int sink_hi = (si < r1 ? si : r1) / bn;         // tile of the last sink column
+  long long w = (long long)r0 - sl;
+  int win_lo = (int)((w < 0 ? 0 : w) / bn);       // tile of the first window column
+  if (win_lo <= sink_hi + 1) {                    // ranges touch or overlap: merge
+    t.lo0 = 0; t.hi0 = diag + 1; t.lo1 = t.hi1 = 0;
+  } else {
+    t.lo0 = 0; t.hi0 = sink_hi + 1; t.lo1 = win_lo; t.hi1 = diag + 1;
+  }
+  return t;
+}
+
+// Sufficient (not necessary) test that KV tile columns [c0, c1] are attended by
+// every row of [r0, r1]; such tiles skip the per-element predicate.
+__host__ __device__ __forceinline__ bool tile_is_full(int r0, int r1, int c0, int c1, int n,
+                                                      int lrow, int si, int sl, int mode) {
+  if (mode == TMX_MODE_NONE) return c1 < n;
+  if (c1 > r0 || c1 >= n) return false;
+  if (mode == TMX_MODE_DENSE_CAUSAL) return true;
+  return (c1 <= si) || ((long long)r1 - c0 <= sl) || (r0 >= lrow);
+}
+
+// ---- error plumbing ---------------------------------------------------------
+void set_cuda_error(cudaError_t e, const char* where);
+#define TMX_CUDA_TRY(expr)                                   \
+  do {                                                       \
+    cudaError_t _e = (expr);                                 \
+    if (_e != cudaSuccess) {                                 \
+      ::tmx::set_cuda_error(_e, #expr);                      \
+      return TMX_ERR_CUDA;                                   \
+    }                                                        \
+  } while (0)
+
+int device_sm_count();
+int check_arch();  // TMX_OK or TMX_ERR_ARCH / TMX_ERR_CUDA
+void count_launch(int n = 1);
+void reset_launch_count();
+
+}  // namespace tmx
