@@ -238,14 +238,14 @@ __global__ void __launch_bounds__(BM * 2, (BM == 64 ? 3 : 1)) attn_mma_kernel(co
     for (int r = 0; r < 2; ++r) {
       float m_new = fmaxf(m_run[r], mx[r]);
       muse[r] = (m_new == -INFINITY) ? 0.f : m_new;       // row fully masked so far
-      alpha[r] = exp2f(m_run[r] - muse[r]);               // m_run == -inf -> 0
+      alpha[r] = fast_exp2(m_run[r] - muse[r]);               // m_run == -inf -> 0
       m_run[r] = m_new;
     }
     float rs[2] = {0.f, 0.f};
 #pragma unroll
     for (int i = 0; i < 8; ++i) {
-      s[i][0] = exp2f(s[i][0] - muse[0]); s[i][1] = exp2f(s[i][1] - muse[0]);
-      s[i][2] = exp2f(s[i][2] - muse[1]); s[i][3] = exp2f(s[i][3] - muse[1]);
+      s[i][0] = fast_exp2(s[i][0] - muse[0]); s[i][1] = fast_exp2(s[i][1] - muse[0]);
+      s[i][2] = fast_exp2(s[i][2] - muse[1]); s[i][3] = fast_exp2(s[i][3] - muse[1]);
       rs[0] += s[i][0] + s[i][1];
       rs[1] += s[i][2] + s[i][3];
     }
@@ -300,7 +300,7 @@ __global__ void __launch_bounds__(BM * 2, (BM == 64 ? 3 : 1)) attn_mma_kernel(co
     }
     return;
   }
-  float inv[2] = {l_run[0] > 0.f ? 1.f / l_run[0] : 0.f, l_run[1] > 0.f ? 1.f / l_run[1] : 0.f};
+  float inv[2] = {l_run[0] > 0.f ? fast_rcp(l_run[0]) : 0.f, l_run[1] > 0.f ? fast_rcp(l_run[1]) : 0.f};
   // stage the bf16 tile through shared memory (K region is free now) for 16-byte row stores
   {
     int ra = warp * 16 + g, rb = ra + 8;
@@ -359,7 +359,7 @@ __global__ void __launch_bounds__(256) combine_kernel(const AttnParams p) {
     float l = 0.f;
     for (int s = 0; s < ns; ++s) {
       float2 ml = p.part_ml[((base + s) * p.Hq + head) * BM + r];
-      float w = (ml.x == -INFINITY) ? 0.f : exp2f(ml.x - mmax);
+      float w = (ml.x == -INFINITY) ? 0.f : fast_exp2(ml.x - mmax);
       l += ml.y * w;
       float4 v = *reinterpret_cast<const float4*>(p.part_o + (((base + s) * p.Hq + head) * BM + r) * kD + c4);
       acc.x += v.x * w; acc.y += v.y * w; acc.z += v.z * w; acc.w += v.w * w;

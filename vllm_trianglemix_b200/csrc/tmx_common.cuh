@@ -112,6 +112,25 @@ __host__ __device__ __forceinline__ bool tile_is_full(int r0, int r1, int c0, in
   return (c1 <= si) || ((long long)r1 - c0 <= sl) || (r0 >= lrow);
 }
 
+// ---- math without --use_fast_math (which would let the compiler assume no infinities) ----
+__device__ __forceinline__ float fast_exp2(float x) {   // ex2.approx: exp2(-inf) = +0
+  float y;
+  asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(y) : "f"(x));
+  return y;
+}
+__device__ __forceinline__ float fast_rcp(float x) {
+  float y;
+  asm("rcp.approx.ftz.f32 %0, %1;" : "=f"(y) : "f"(x));
+  return y;
+}
+__host__ __device__ __forceinline__ bool is_neg_inf(float x) {
+#ifdef __CUDA_ARCH__
+  return __float_as_uint(x) == 0xff800000u;
+#else
+  return x < 0 && (x - x) != 0.0f && x == x * 2.0f;
+#endif
+}
+
 // ---- error plumbing ---------------------------------------------------------
 void set_cuda_error(cudaError_t e, const char* where);
 #define TMX_CUDA_TRY(expr)                                   \

@@ -86,7 +86,7 @@ __global__ void rewrite_neg_inf_kernel(T* __restrict__ out, const T* __restrict_
   for (; idx < numel; idx += stride) {
     T x = in[idx];
     float xf = (float)x;
-    out[idx] = (isinf(xf) && xf < 0.f) ? f : x;   // only -inf is rewritten
+    out[idx] = is_neg_inf(xf) ? f : x;   // only -inf is rewritten
   }
 }
 
@@ -112,7 +112,7 @@ bits_from_additive_kernel(uint32_t* __restrict__ out, long long row_stride_words
       if (wbase + w < row_stride_words && c < n) {
         float x = (float)src[c];
         on = (x == 0.0f);
-        bad += (!on && !(isinf(x) && x < 0.0f));
+        bad += (!on && !is_neg_inf(x));
       }
       uint32_t word = __ballot_sync(0xffffffffu, on);
       if (w == lane) mine = word;
