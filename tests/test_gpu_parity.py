@@ -111,7 +111,8 @@ def test_bits_from_additive_and_rewrite(tmx, ops):
         assert int(bad.item()) == 0
         assert torch.equal(bits, ops.mask_bits(n, si, sl, last, "triangle", dev))
         rew = tmx.AscendNPUTriangleMixOptimizer.optimize_mask_for_npu(add)
-        assert not torch.isinf(rew).any()
+        if dtype != torch.float16:      # -1e6 overflows to -inf in fp16, in the reference too
+            assert not torch.isinf(rew).any()
         want = orc.rewrite_neg_inf(orc.additive(orc.mask_closed(n, si, sl, last, orc.TRIANGLE)))
         assert np.array_equal(rew.float().cpu().numpy(), want.astype(np.float32) if dtype == torch.float32
                               else torch.from_numpy(want).to(dtype).float().numpy())
