@@ -1,5 +1,6 @@
 // C-ABI entry points that are not kernels themselves: error strings, launch
 // accounting, workspace sizing and the tmx_prefill_attn dispatcher.
+#include <cstdlib>
 #include <mutex>
 #include <string>
 #include "tmx_attn.cuh"
@@ -27,6 +28,15 @@ int device_sm_count() {
     if (sms <= 0) sms = 148;
   }
   return sms;
+}
+
+int sm100_variant() {
+  static int v = -1;
+  if (v < 0) {
+    const char* e = std::getenv("TMX_SM100_VARIANT");
+    v = e ? (std::atoi(e) & 3) : 0;
+  }
+  return v;
 }
 
 int check_arch() {
@@ -58,7 +68,7 @@ Plan make_plan(int B, int total_T, int max_seqlen, int Hq, int last, int mode, i
   pl.kernel = (kernel == TMX_KERNEL_AUTO) ? TMX_KERNEL_MMA : kernel;
   pl.bn = 64;
   pl.bm = (mode == TMX_MODE_TRIANGLE) ? 64 : 128;
-  if (pl.kernel == TMX_KERNEL_TCGEN05) { pl.bm = 128; pl.bn = 128; }
+  if (pl.kernel == TMX_KERNEL_TCGEN05) { pl.bm = 128; pl.bn = sm100_block_n(sm100_variant()); }
   pl.n_slots = total_T / pl.bm + B;
   pl.last_tiles = 0; pl.nsplit_max = 0;
   if (pl.kernel == TMX_KERNEL_MMA && mode == TMX_MODE_TRIANGLE) {
@@ -130,7 +140,7 @@ extern "C" int tmx_prefill_attn(void* out, const void* q, const void* k, const v
   auto mis = [](const void* p) { return (reinterpret_cast<uintptr_t>(p) & 15u) != 0; };
   if (mis(out) || mis(q) || mis(k) || mis(v) || (q_stride_t % 8) || (kv_stride_t % 8) || (o_stride_t % 8))
     return TMX_ERR_ALIGNMENT;
-  if (bitmask && (bitmask_stride_words * 32 < max_seqlen || bitmask_stride_words % 2)) return TMX_ERR_BAD_SHAPE;
+  if (bitmask && (bitmask_stride_words * 32 < max_seqlen || bitmask_stride_words % 4)) return TMX_ERR_BAD_SHAPE;
   int st = check_arch();
   if (st != TMX_OK) return st;
 
@@ -155,6 +165,6 @@ extern "C" int tmx_prefill_attn(void* out, const void* q, const void* k, const v
   st = build_slots(reinterpret_cast<SlotInfo*>(ws + pl.off_slots), pl.n_slots, cu_seqlens, B,
                    max_seqlen, pl.bm, pl.bn, si, sl, last, mode, s);
   if (st != TMX_OK) return st;
-  if (pl.kernel == TMX_KERNEL_TCGEN05) return launch_attn_sm100(p, s);
+  if (pl.kernel == TMX_KERNEL_TCGEN05) return launch_attn_sm100(p, sm100_variant(), s);
   return launch_attn_mma(p, pl.bm, s);
 }

@@ -26,6 +26,8 @@ struct AttnParams {
 int build_slots(SlotInfo* slots, int n_slots, const int* cu, int B, int max_seqlen, int bm, int bn,
                 int si, int sl, int last, int mode, cudaStream_t s);
 int launch_attn_mma(const AttnParams& p, int bm, cudaStream_t s);
-int launch_attn_sm100(const AttnParams& p, cudaStream_t s);
+int launch_attn_sm100(const AttnParams& p, int variant, cudaStream_t s);
+int sm100_block_n(int variant);
+int sm100_variant();   // TMX_SM100_VARIANT env (developer switch), default 0
 
 }  // namespace tmx
