@@ -34,7 +34,7 @@ int sm100_variant() {
   static int v = -1;
   if (v < 0) {
     const char* e = std::getenv("TMX_SM100_VARIANT");
-    v = e ? (std::atoi(e) & 3) : 0;
+    v = e ? (std::atoi(e) & 3) : 1;   // BN 64, P in TMEM: fastest measured
   }
   return v;
 }
@@ -63,9 +63,14 @@ struct Plan {
   size_t off_slots, off_part_o, off_part_ml, total;
 };
 
-Plan make_plan(int B, int total_T, int max_seqlen, int Hq, int last, int mode, int kernel) {
+Plan make_plan(int B, int total_T, int max_seqlen, int Hq, int Hkv, int last, int mode, int kernel) {
   Plan pl{};
-  pl.kernel = (kernel == TMX_KERNEL_AUTO) ? TMX_KERNEL_MMA : kernel;
+  // AUTO: the tcgen05 kernel serves every tensor-bound case it can pair heads for (dense-causal
+  // and unmasked layers); triangle layers (HBM-bound, split last tile) stay on the mma.sync kernel.
+  const bool pairable = Hkv > 0 && Hq % Hkv == 0 && (Hq / Hkv) % 2 == 0;
+  pl.kernel = kernel;
+  if (kernel == TMX_KERNEL_AUTO)
+    pl.kernel = (pairable && mode != TMX_MODE_TRIANGLE) ? TMX_KERNEL_TCGEN05 : TMX_KERNEL_MMA;
   pl.bn = 64;
   pl.bm = (mode == TMX_MODE_TRIANGLE) ? 64 : 128;
   if (pl.kernel == TMX_KERNEL_TCGEN05) { pl.bm = 128; pl.bn = sm100_block_n(sm100_variant()); }
@@ -115,9 +120,9 @@ extern "C" int tmx_last_launch_count(void) { return g_launches; }
 
 extern "C" size_t tmx_attn_workspace_bytes(int B, int total_T, int max_seqlen, int Hq, int Hkv,
                                            int D, int si, int sl, int last, int mode, int kernel) {
-  (void)Hkv; (void)D; (void)si; (void)sl;
+  (void)D; (void)si; (void)sl;
   if (B <= 0 || total_T <= 0) return 256;
-  return make_plan(B, total_T, max_seqlen, Hq, last, mode, kernel).total;
+  return make_plan(B, total_T, max_seqlen, Hq, Hkv, last, mode, kernel).total;
 }
 
 extern "C" int tmx_prefill_attn(void* out, const void* q, const void* k, const void* v,
@@ -144,7 +149,7 @@ extern "C" int tmx_prefill_attn(void* out, const void* q, const void* k, const v
   int st = check_arch();
   if (st != TMX_OK) return st;
 
-  Plan pl = make_plan(B, total_T, max_seqlen, Hq, last, mode, kernel);
+  Plan pl = make_plan(B, total_T, max_seqlen, Hq, Hkv, last, mode, kernel);
   if (!workspace || workspace_bytes < pl.total || mis(workspace)) return TMX_ERR_WORKSPACE;
   cudaStream_t s = (cudaStream_t)stream;
   uint8_t* ws = static_cast<uint8_t*>(workspace);
