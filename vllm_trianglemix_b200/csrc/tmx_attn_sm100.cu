@@ -4,16 +4,17 @@
 // head-group reuse: every K/V tile is fetched once for 256 query rows).  10 warps:
 //   warps 0-3  softmax group A (head h0):   one thread per query row, TMEM lanes 0..127
 //   warps 4-7  softmax group B (head h0+1)
-//   warp  8    TMA producer: Q once, then the K/V tiles the block index lists (ring of stages)
+//   warp  8    TMA producer: Q once, then the K/V tiles the block index lists (rings of stages)
 //   warp  9    MMA issuer (one elected thread): S = Q K^T into TMEM, O += P V
-// TMEM (512 columns): S_A | S_B | O_A | O_B, 128 fp32 columns each.  P (bf16) either
-// overwrites the first half of its S columns (kPTmem, A operand read from TMEM) or goes to
-// shared memory in the 128B-swizzled K-major layout.  The issue order
-//   S_A(0) S_B(0) { PV_A(j) S_A(j+1) PV_B(j) S_B(j+1) }_j
-// lets group A's softmax overlap group B's MMAs and vice versa.  The running max is only
-// refreshed (and O rescaled in TMEM) when it grows by more than 2^8, so the correction is
-// off the common path.  Fully masked KV tiles are never loaded; only PARTIAL tiles evaluate
-// the mask predicate.
+// KV tiles are 64 keys.  TMEM (512 columns): S_A[2] | S_B[2] (64 fp32 columns each, double
+// buffered) | O_A | O_B (128 columns each).  P (bf16) overwrites the first half of the S
+// buffer it came from and is read by the MMA straight from TMEM.  Issue order
+//   S_A(0) S_B(0) S_A(1) S_B(1) { PV_A(j) S_A(j+2) PV_B(j) S_B(j+2) }_j
+// so a group's next scores are already in TMEM when it finishes a tile: the softmax warps
+// never wait for their own MMAs, and the tensor pipe works on one group while the other
+// exponentiates.  The running max is only refreshed (and O rescaled in TMEM) when it grows
+// by more than 2^8, so the correction is off the common path.  Fully masked KV tiles are
+// never loaded; only PARTIAL tiles evaluate the mask predicate.
 //
 // Replaces vllm/attention/ascend_trianglemix.py:86-106 of the reference for dense-causal
 // layers (and for any triangle setting through the same block index).
@@ -28,34 +29,32 @@ namespace {
 
 constexpr int kD = 128;
 constexpr int kBM = 128;
+constexpr int kBN = 64;
 constexpr int kThreads = 320;
 constexpr int kQBytes = 2 * 2 * kBM * 128;        // 2 heads x 2 panels of [128 rows][64 d] = 64 KB
-
-template <int BN, bool kPTmem> struct Cfg {
-  static constexpr int kStages = (BN == 64) ? 3 : (kPTmem ? 2 : 1);
-  static constexpr int kPanelBytes = BN * 128;                 // [BN keys][64 d] bf16
-  static constexpr int kTileBytes = 2 * kPanelBytes;           // K or V tile
-  static constexpr int kPBytes = kPTmem ? 0 : 2 * (BN / 64) * (kBM * 128);   // 2 heads
-  static constexpr int kOffK = kQBytes;
-  static constexpr int kOffV = kOffK + kStages * kTileBytes;
-  static constexpr int kOffP = kOffV + kStages * kTileBytes;
-  static constexpr int kOffBar = kOffP + kPBytes;
-  static constexpr int kNumBars = 1 + 4 * kStages + 2 + 2 + 2;
-  static constexpr int kSmem = kOffBar + kNumBars * 8 + 16 + 1024;   // + alignment slack
-};
+constexpr int kKStages = 4, kVStages = 3;
+constexpr int kPanelBytes = kBN * 128;            // [64 keys][64 d] bf16 = 8 KB
+constexpr int kTileBytes = 2 * kPanelBytes;       // K or V tile = 16 KB
+constexpr int kOffK = kQBytes;
+constexpr int kOffV = kOffK + kKStages * kTileBytes;
+constexpr int kOffBar = kOffV + kVStages * kTileBytes;
 
 // barrier indices
-template <int BN, bool kPTmem> struct Bars {
-  static constexpr int S = Cfg<BN, kPTmem>::kStages;
-  static constexpr int q_full = 0;
-  static constexpr int k_full = 1;            // [S]
-  static constexpr int v_full = 1 + S;        // [S]
-  static constexpr int k_empty = 1 + 2 * S;   // [S]
-  static constexpr int v_empty = 1 + 3 * S;   // [S]
-  static constexpr int s_full = 1 + 4 * S;    // [2]
-  static constexpr int p_ready = 3 + 4 * S;   // [2]
-  static constexpr int o_full = 5 + 4 * S;    // [2]
-};
+constexpr int bQFull = 0;
+constexpr int bKFull = 1;                         // [kKStages]
+constexpr int bKEmpty = bKFull + kKStages;        // [kKStages]
+constexpr int bVFull = bKEmpty + kKStages;        // [kVStages]
+constexpr int bVEmpty = bVFull + kVStages;        // [kVStages]
+constexpr int bSFull = bVEmpty + kVStages;        // [2 groups][2 buffers]
+constexpr int bPReady = bSFull + 4;               // [2 groups][2 buffers], 4 arrivals (one per warp)
+constexpr int bPVDone = bPReady + 4;              // [2]: completes after every PV of the group
+constexpr int bOFull = bPVDone + 2;               // [2]: the group's last PV has completed
+constexpr int kNumBars = bOFull + 2;
+constexpr int kSmem = kOffBar + kNumBars * 8 + 16 + 1024;   // + alignment slack
+
+// TMEM columns
+constexpr uint32_t kColS = 0;      // + g * 128 + buf * 64
+constexpr uint32_t kColO = 256;    // + g * 128
 
 struct TmaMaps {
   CUtensorMap q, k, v;
@@ -107,40 +106,32 @@ int make_map(CUtensorMap* m, const void* base, long long rows, long long cols, l
   return TMX_OK;
 }
 
-template <int BN, bool kPTmem>
-int launch_t(const AttnParams& p, cudaStream_t s) {
-  using C = Cfg<BN, kPTmem>;
+}  // namespace
+
+int sm100_block_n(int) { return kBN; }
+
+int launch_attn_sm100(const AttnParams& p, int variant, cudaStream_t s) {
+  if ((p.Hq / p.Hkv) % 2 != 0) return TMX_ERR_UNSUPPORTED;   // needs two query heads per KV head
+  if (!(p.scale_log2 > 0.f)) return TMX_ERR_UNSUPPORTED;     // row max is taken on raw scores
   static bool attr_set = false;
   if (!attr_set) {
-    TMX_CUDA_TRY(cudaFuncSetAttribute(attn_sm100_kernel<BN, kPTmem>,
-                                      cudaFuncAttributeMaxDynamicSharedMemorySize, C::kSmem));
+    TMX_CUDA_TRY(cudaFuncSetAttribute(attn_sm100_kernel<0>, cudaFuncAttributeMaxDynamicSharedMemorySize, kSmem));
+    TMX_CUDA_TRY(cudaFuncSetAttribute(attn_sm100_kernel<2>, cudaFuncAttributeMaxDynamicSharedMemorySize, kSmem));
     attr_set = true;
   }
   TmaMaps maps;
   int st = make_map(&maps.q, p.q, p.total_T, (long long)p.Hq * kD, p.q_stride, kBM);
-  if (st == TMX_OK) st = make_map(&maps.k, p.k, p.total_T, (long long)p.Hkv * kD, p.kv_stride, BN);
-  if (st == TMX_OK) st = make_map(&maps.v, p.v, p.total_T, (long long)p.Hkv * kD, p.kv_stride, BN);
+  if (st == TMX_OK) st = make_map(&maps.k, p.k, p.total_T, (long long)p.Hkv * kD, p.kv_stride, kBN);
+  if (st == TMX_OK) st = make_map(&maps.v, p.v, p.total_T, (long long)p.Hkv * kD, p.kv_stride, kBN);
   if (st != TMX_OK) return st;
   dim3 grid((unsigned)p.n_slots, (unsigned)(p.Hq / 2));
-  attn_sm100_kernel<BN, kPTmem><<<grid, kThreads, C::kSmem, s>>>(p, maps);
+  if (variant & 1)   // a quarter of the exponentials on the FMA pipe
+    attn_sm100_kernel<2><<<grid, kThreads, kSmem, s>>>(p, maps);
+  else
+    attn_sm100_kernel<0><<<grid, kThreads, kSmem, s>>>(p, maps);
   count_launch();
   TMX_CUDA_TRY(cudaGetLastError());
   return TMX_OK;
-}
-
-}  // namespace
-
-int sm100_block_n(int variant) { return (variant & 1) ? 64 : 128; }
-
-// variant: bit0 = BN 64 (else 128), bit1 = P through shared memory (else TMEM)
-int launch_attn_sm100(const AttnParams& p, int variant, cudaStream_t s) {
-  if ((p.Hq / p.Hkv) % 2 != 0) return TMX_ERR_UNSUPPORTED;   // needs two query heads per KV head
-  switch (variant & 3) {
-    case 0: return launch_t<128, true>(p, s);
-    case 1: return launch_t<64, true>(p, s);
-    case 2: return launch_t<128, false>(p, s);
-    default: return launch_t<64, false>(p, s);
-  }
 }
 
 }  // namespace tmx

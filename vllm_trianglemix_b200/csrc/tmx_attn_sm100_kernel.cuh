@@ -4,20 +4,31 @@
 namespace tmx {
 namespace {
 
-template <int BN, bool kPTmem>
+// 2^t for t <= ~8 on the FMA/ALU pipes (no MUFU): round-to-nearest split t = n + f,
+// f in [-0.5, 0.5], cubic minimax for 2^f (max rel. error 7.5e-5, far below bf16's 2^-9),
+// then n is added into the exponent field.
+__device__ __forceinline__ float exp2_poly(float t) {
+  t = fmaxf(t, -126.0f);
+  const float r = t + 12582912.0f;          // 1.5 * 2^23: low mantissa bits of r hold n
+  const float f = t - (r - 12582912.0f);
+  float pl = fmaf(0.0551716685f, f, 0.2426111251f);
+  pl = fmaf(pl, f, 0.6932609677f);
+  pl = fmaf(pl, f, 0.9999280572f);
+  return __int_as_float(__float_as_int(pl) + (__float_as_int(r) << 23));
+}
+
+template <int kEmu>
 __global__ void __launch_bounds__(kThreads, 1)
 attn_sm100_kernel(const AttnParams p, const __grid_constant__ TmaMaps maps) {
-  using C = Cfg<BN, kPTmem>;
-  using B = Bars<BN, kPTmem>;
-  constexpr int S = C::kStages;
   extern __shared__ uint8_t smem_raw[];
   const uint32_t smem_base = (ptx::smem_u32(smem_raw) + 1023u) & ~1023u;   // SWIZZLE_128B: 1024-byte atoms
-  const uint32_t sQ = smem_base, sK = smem_base + C::kOffK, sV = smem_base + C::kOffV;
-  const uint32_t sP = smem_base + C::kOffP, sBar = smem_base + C::kOffBar;
-  const uint32_t sTmemPtr = sBar + C::kNumBars * 8;
+  const uint32_t sQ = smem_base, sK = smem_base + kOffK, sV = smem_base + kOffV;
+  const uint32_t sBar = smem_base + kOffBar;
+  const uint32_t sTmemPtr = sBar + kNumBars * 8;
   auto bar = [&](int i) { return sBar + 8u * (uint32_t)i; };
 
-  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int warp = __shfl_sync(0xffffffffu, (int)(threadIdx.x >> 5), 0);   // provably warp-uniform
+  const int lane = threadIdx.x & 31;
 
   // ---- work item (uniform per CTA) -------------------------------------------
   const SlotInfo slot = p.slots[p.n_slots - 1 - blockIdx.x];      // descending: longest first
@@ -35,16 +46,14 @@ attn_sm100_kernel(const AttnParams p, const __grid_constant__ TmaMaps maps) {
   // ---- setup -------------------------------------------------------------------
   if (warp == 8 && lane == 0) {
     ptx::prefetch_tmap(&maps.q); ptx::prefetch_tmap(&maps.k); ptx::prefetch_tmap(&maps.v);
-    ptx::mbar_init(bar(B::q_full), 1);
-    for (int s = 0; s < S; ++s) {
-      ptx::mbar_init(bar(B::k_full + s), 1); ptx::mbar_init(bar(B::v_full + s), 1);
-      ptx::mbar_init(bar(B::k_empty + s), 1); ptx::mbar_init(bar(B::v_empty + s), 1);
+    ptx::mbar_init(bar(bQFull), 1);
+    for (int s = 0; s < kKStages; ++s) { ptx::mbar_init(bar(bKFull + s), 1); ptx::mbar_init(bar(bKEmpty + s), 1); }
+    for (int s = 0; s < kVStages; ++s) { ptx::mbar_init(bar(bVFull + s), 1); ptx::mbar_init(bar(bVEmpty + s), 1); }
+    for (int i = 0; i < 4; ++i) {
+      ptx::mbar_init(bar(bSFull + i), 1);
+      ptx::mbar_init(bar(bPReady + i), 4);       // one arrive per softmax warp of the group
     }
-    for (int g = 0; g < 2; ++g) {
-      ptx::mbar_init(bar(B::s_full + g), 1);
-      ptx::mbar_init(bar(B::p_ready + g), 128);
-      ptx::mbar_init(bar(B::o_full + g), 1);
-    }
+    for (int g = 0; g < 2; ++g) { ptx::mbar_init(bar(bPVDone + g), 1); ptx::mbar_init(bar(bOFull + g), 1); }
     ptx::fence_barrier_init();
   }
   if (warp == 9) ptx::tmem_alloc(sTmemPtr, 512);
@@ -54,89 +63,112 @@ attn_sm100_kernel(const AttnParams p, const __grid_constant__ TmaMaps maps) {
   uint32_t tmem_base;
   asm volatile("ld.shared.b32 %0, [%1];" : "=r"(tmem_base) : "r"(sTmemPtr));
 
-  constexpr uint32_t kIdescS = ptx::instr_desc_bf16(128, BN, false);
-  constexpr uint32_t kIdescO = ptx::instr_desc_bf16(128, 128, true);
-
   if (warp == 8) {
     // =========================== TMA producer ===========================
-    if (lane == 0) {
-      ptx::mbar_expect_tx(bar(B::q_full), kQBytes);
+    // Load order follows consumption: K(0) K(1) { V(j) K(j+2) }_j
+    if (ptx::elect_one()) {
+      ptx::mbar_expect_tx(bar(bQFull), kQBytes);
       for (int g = 0; g < 2; ++g)
         for (int pnl = 0; pnl < 2; ++pnl)
-          ptx::tma_load_2d(sQ + (g * 2 + pnl) * (kBM * 128), &maps.q, bar(B::q_full),
+          ptx::tma_load_2d(sQ + (g * 2 + pnl) * (kBM * 128), &maps.q, bar(bQFull),
                            (h0 + g) * kD + pnl * 64, seq_start + r0);
+      auto load_k = [&](int it) {
+        const int st = it % kKStages, round = it / kKStages;
+        if (round > 0) ptx::mbar_wait(bar(bKEmpty + st), (round - 1) & 1);
+        ptx::mbar_expect_tx(bar(bKFull + st), kTileBytes);
+        const int row = seq_start + tile_of(it) * kBN;
+        for (int pnl = 0; pnl < 2; ++pnl)
+          ptx::tma_load_2d(sK + st * kTileBytes + pnl * kPanelBytes, &maps.k, bar(bKFull + st),
+                           kvh * kD + pnl * 64, row);
+      };
+      auto load_v = [&](int it) {
+        const int st = it % kVStages, round = it / kVStages;
+        if (round > 0) ptx::mbar_wait(bar(bVEmpty + st), (round - 1) & 1);
+        ptx::mbar_expect_tx(bar(bVFull + st), kTileBytes);
+        const int row = seq_start + tile_of(it) * kBN;
+        for (int pnl = 0; pnl < 2; ++pnl)
+          ptx::tma_load_2d(sV + st * kTileBytes + pnl * kPanelBytes, &maps.v, bar(bVFull + st),
+                           kvh * kD + pnl * 64, row);
+      };
+      load_k(0);
+      if (total > 1) load_k(1);
       for (int it = 0; it < total; ++it) {
-        const int st = it % S, round = it / S;
-        const int row = seq_start + tile_of(it) * BN;
-        if (round > 0) ptx::mbar_wait(bar(B::k_empty + st), (round - 1) & 1);
-        ptx::mbar_expect_tx(bar(B::k_full + st), C::kTileBytes);
-        for (int pnl = 0; pnl < 2; ++pnl)
-          ptx::tma_load_2d(sK + st * C::kTileBytes + pnl * C::kPanelBytes, &maps.k, bar(B::k_full + st),
-                           kvh * kD + pnl * 64, row);
-        if (round > 0) ptx::mbar_wait(bar(B::v_empty + st), (round - 1) & 1);
-        ptx::mbar_expect_tx(bar(B::v_full + st), C::kTileBytes);
-        for (int pnl = 0; pnl < 2; ++pnl)
-          ptx::tma_load_2d(sV + st * C::kTileBytes + pnl * C::kPanelBytes, &maps.v, bar(B::v_full + st),
-                           kvh * kD + pnl * 64, row);
+        load_v(it);
+        if (it + 2 < total) load_k(it + 2);
       }
     }
     __syncwarp();
   } else if (warp == 9) {
     // =========================== MMA issuer ===========================
-    if (lane == 0) {
-      // S_g(j) = Q_g K(j)^T : 8 k-steps of 16 over d; Q/K panels hold 64 d each (4 k-steps per panel)
-      auto issue_s = [&](int g, int st) {
-        const uint32_t d_tmem = tmem_base + (uint32_t)(g * 128);
+    // The whole warp runs the loop (warp-uniform control flow keeps descriptors and
+    // addresses in uniform registers); one elected lane issues the tcgen05 instructions.
+    const uint32_t tb = __shfl_sync(0xffffffffu, tmem_base, 0);
+    const int ntot = __shfl_sync(0xffffffffu, total, 0);
+    constexpr uint32_t kIdescS = ptx::instr_desc_bf16(128, kBN, false);
+    constexpr uint32_t kIdescO = ptx::instr_desc_bf16(128, 128, true);
+    const uint64_t dQ = ptx::smem_desc(sQ, 16, 1024);
+    const uint64_t dK = ptx::smem_desc(sK, 16, 1024);
+    const uint64_t dV = ptx::smem_desc(sV, kPanelBytes, 1024);
+
+    // S_g(tile in K stage kst) -> S buffer `buf`: 8 k-steps of 16 over d (panels of 64 d)
+    auto issue_s = [&](int g, int buf, int kst) {
+      const uint32_t d_tmem = tb + kColS + (uint32_t)(g * 128 + buf * 64);
+      const uint64_t qa = dQ + (uint64_t)((g * 2 * (kBM * 128)) >> 4);
+      const uint64_t kb = dK + (uint64_t)((kst * kTileBytes) >> 4);
 #pragma unroll
-        for (int ks = 0; ks < 8; ++ks) {
-          const uint32_t qa = sQ + (g * 2 + (ks >> 2)) * (kBM * 128) + (ks & 3) * 32;
-          const uint32_t kb = sK + st * C::kTileBytes + (ks >> 2) * C::kPanelBytes + (ks & 3) * 32;
-          ptx::mma_ss(d_tmem, ptx::smem_desc(qa, 16, 1024), ptx::smem_desc(kb, 16, 1024), kIdescS, ks > 0);
-        }
-      };
-      // O_g += P_g V(j) : BN/16 k-steps over keys; V is MN-major (d contiguous): panels of 64 d
-      auto issue_pv = [&](int g, int st, bool acc) {
-        const uint32_t d_tmem = tmem_base + 256u + (uint32_t)(g * 128);
-#pragma unroll
-        for (int ks = 0; ks < BN / 16; ++ks) {
-          const uint32_t vb = sV + st * C::kTileBytes + ks * 2048;
-          const uint64_t bdesc = ptx::smem_desc(vb, C::kPanelBytes, 1024);
-          if (kPTmem) {
-            ptx::mma_ts(d_tmem, tmem_base + (uint32_t)(g * 128 + ks * 8), bdesc, kIdescO, acc || ks > 0);
-          } else {
-            const uint32_t pa = sP + g * (C::kPBytes / 2) + (ks >> 2) * (kBM * 128) + (ks & 3) * 32;
-            ptx::mma_ss(d_tmem, ptx::smem_desc(pa, 16, 1024), bdesc, kIdescO, acc || ks > 0);
-          }
-        }
-      };
-      ptx::mbar_wait(bar(B::q_full), 0);
-      ptx::mbar_wait(bar(B::k_full + 0), 0);
-      ptx::tc_fence_after();
-      issue_s(0, 0); ptx::mma_commit(bar(B::s_full + 0));
-      issue_s(1, 0); ptx::mma_commit(bar(B::s_full + 1));
-      ptx::mma_commit(bar(B::k_empty + 0));
-      for (int j = 0; j < total; ++j) {
-        const int st = j % S, ph = (j / S) & 1;
-        const int st1 = (j + 1) % S, ph1 = ((j + 1) / S) & 1;
-        const bool more = j + 1 < total;
-        ptx::mbar_wait(bar(B::v_full + st), ph);
-        for (int g = 0; g < 2; ++g) {
-          ptx::mbar_wait(bar(B::p_ready + g), j & 1);
-          ptx::tc_fence_after();
-          issue_pv(g, st, j > 0);
-          if (g == 1) ptx::mma_commit(bar(B::v_empty + st));
-          if (more) {
-            if (g == 0) { ptx::mbar_wait(bar(B::k_full + st1), ph1); ptx::tc_fence_after(); }
-            issue_s(g, st1);
-            ptx::mma_commit(bar(B::s_full + g));
-            if (g == 1) ptx::mma_commit(bar(B::k_empty + st1));
-          } else {
-            ptx::mma_commit(bar(B::o_full + g));
-          }
-        }
+      for (int ks = 0; ks < 8; ++ks) {
+        const uint32_t qo = ((ks >> 2) * (kBM * 128) + (ks & 3) * 32) >> 4;
+        const uint32_t ko = ((ks >> 2) * kPanelBytes + (ks & 3) * 32) >> 4;
+        ptx::mma_ss(d_tmem, qa + qo, kb + ko, kIdescS, ks > 0);
       }
+    };
+    // O_g += P_g V: 4 k-steps of 16 keys; P (bf16) read from the S buffer it overwrote
+    auto issue_pv = [&](int g, int buf, int vst, bool acc) {
+      const uint32_t d_tmem = tb + kColO + (uint32_t)(g * 128);
+      const uint32_t a_tmem = tb + kColS + (uint32_t)(g * 128 + buf * 64);
+      const uint64_t vb = dV + (uint64_t)((vst * kTileBytes) >> 4);
+#pragma unroll
+      for (int ks = 0; ks < kBN / 16; ++ks)
+        ptx::mma_ts(d_tmem, a_tmem + (uint32_t)(ks * 8), vb + (uint64_t)((ks * 2048) >> 4), kIdescO,
+                    acc || ks > 0);
+    };
+
+    ptx::mbar_wait(bar(bQFull), 0);
+    for (int t = 0; t < 2 && t < ntot; ++t) {
+      ptx::mbar_wait(bar(bKFull + t), 0);
+      ptx::tc_fence_after();
+      if (ptx::elect_one()) {
+        issue_s(0, t, t); ptx::mma_commit(bar(bSFull + 0 + t));
+        issue_s(1, t, t); ptx::mma_commit(bar(bSFull + 2 + t));
+        ptx::mma_commit(bar(bKEmpty + t));
+      }
+      __syncwarp();
     }
-    __syncwarp();
+    int vst = 0, vph = 0, kst = 2 % kKStages, kph = 0;     // stage / parity of V(j) and K(j+2)
+    for (int j = 0; j < ntot; ++j) {
+      const int buf = j & 1, pph = (j >> 1) & 1;
+      const bool more = j + 2 < ntot;
+      ptx::mbar_wait(bar(bVFull + vst), vph);
+#pragma unroll
+      for (int g = 0; g < 2; ++g) {
+        ptx::mbar_wait(bar(bPReady + g * 2 + buf), pph);
+        if (more && g == 0) ptx::mbar_wait(bar(bKFull + kst), kph);
+        ptx::tc_fence_after();
+        if (ptx::elect_one()) {
+          issue_pv(g, buf, vst, j > 0);
+          ptx::mma_commit(bar(j + 1 < ntot ? bPVDone + g : bOFull + g));
+          if (g == 1) ptx::mma_commit(bar(bVEmpty + vst));
+          if (more) {
+            issue_s(g, buf, kst);
+            ptx::mma_commit(bar(bSFull + g * 2 + buf));
+            if (g == 1) ptx::mma_commit(bar(bKEmpty + kst));
+          }
+        }
+        __syncwarp();
+      }
+      if (++vst == kVStages) { vst = 0; vph ^= 1; }
+      if (++kst == kKStages) { kst = 0; kph ^= 1; }
+    }
   } else {
     // =========================== softmax groups ===========================
     const int g = warp >> 2;                       // 0: head h0, 1: head h0 + 1
@@ -144,49 +176,56 @@ attn_sm100_kernel(const AttnParams p, const __grid_constant__ TmaMaps maps) {
     const int i = r0 + row_in_tile;                // query row inside the sequence
     const int head = h0 + g;
     const uint32_t lane_base = (uint32_t)((warp & 3) * 32) << 16;
-    const uint32_t tS = tmem_base + lane_base + (uint32_t)(g * 128);
-    const uint32_t tO = tmem_base + lane_base + 256u + (uint32_t)(g * 128);
-    const float sc = p.scale_log2;
-    float m_ref = -INFINITY, l_run = 0.f;
+    const uint32_t tSg = tmem_base + lane_base + kColS + (uint32_t)(g * 128);
+    const uint32_t tO = tmem_base + lane_base + kColO + (uint32_t)(g * 128);
+    const float sc = p.scale_log2;                 // > 0 (checked by the launcher)
+    float m_ref = -INFINITY, l_run = 0.f;          // running max (scaled, log2 domain) and row sum
     const uint32_t* bm_row = p.bitmask ? p.bitmask + (long long)min(i, n - 1) * p.bitmask_stride : nullptr;
 
     for (int j = 0; j < total; ++j) {
-      ptx::mbar_wait(bar(B::s_full + g), j & 1);
+      const int buf = j & 1;
+      const uint32_t tS = tSg + (uint32_t)(buf * 64);
+      ptx::mbar_wait(bar(bSFull + g * 2 + buf), (j >> 1) & 1);
       ptx::tc_fence_after();
-      const int c0 = tile_of(j) * BN;
+      uint32_t xr[kBN];
+      ptx::tmem_ld32(tS, *reinterpret_cast<uint32_t(*)[32]>(&xr[0]));
+      ptx::tmem_ld32(tS + 32, *reinterpret_cast<uint32_t(*)[32]>(&xr[32]));
+      ptx::tc_wait_ld();
+      float x[kBN];
+#pragma unroll
+      for (int e = 0; e < kBN; ++e) x[e] = __uint_as_float(xr[e]);
+
+      const int c0 = tile_of(j) * kBN;
       const bool full = bm_row == nullptr &&
-                        tile_is_full(r0, r1, c0, c0 + BN - 1, n, lrow, p.si, p.sl, p.mode);
-      float x[BN];
-#pragma unroll
-      for (int c = 0; c < BN / 32; ++c) {
-        uint32_t r[32];
-        ptx::tmem_ld32(tS + c * 32, r);
-        ptx::tc_wait_ld();
-#pragma unroll
-        for (int e = 0; e < 32; ++e) x[c * 32 + e] = __uint_as_float(r[e]) * sc;
-      }
+                        tile_is_full(r0, r1, c0, c0 + kBN - 1, n, lrow, p.si, p.sl, p.mode);
       if (!full) {
         if (bm_row == nullptr) {
 #pragma unroll
-          for (int e = 0; e < BN; ++e)
+          for (int e = 0; e < kBN; ++e)
             x[e] = attends(i, c0 + e, n, lrow, p.si, p.sl, p.mode) ? x[e] : -INFINITY;
         } else {
 #pragma unroll
-          for (int w = 0; w < BN / 32; ++w) {
+          for (int w = 0; w < kBN / 32; ++w) {
             const uint32_t bits = bm_row[(c0 >> 5) + w];
 #pragma unroll
             for (int e = 0; e < 32; ++e) x[w * 32 + e] = ((bits >> e) & 1u) ? x[w * 32 + e] : -INFINITY;
           }
         }
       }
-      float mx = -INFINITY;
+      float mx0 = x[0], mx1 = x[1], mx2 = x[2], mx3 = x[3];
 #pragma unroll
-      for (int e = 0; e < BN; ++e) mx = fmaxf(mx, x[e]);
-      const float m_new = fmaxf(m_ref, mx);
+      for (int e = 4; e < kBN; e += 4) {
+        mx0 = fmaxf(mx0, x[e]); mx1 = fmaxf(mx1, x[e + 1]);
+        mx2 = fmaxf(mx2, x[e + 2]); mx3 = fmaxf(mx3, x[e + 3]);
+      }
+      const float m_new = fmaxf(m_ref, fmaxf(fmaxf(mx0, mx1), fmaxf(mx2, mx3)) * sc);
       // refresh the reference max lazily: only when some row of the warp grew by > 2^8
       const bool grow = (m_new > m_ref + 8.0f) || (m_ref == -INFINITY && m_new > -INFINITY);
       if (__any_sync(0xffffffffu, grow)) {
         if (j > 0) {
+          // O holds tiles 0..j-1 once PV(j-1) has completed; PV(j) cannot start before our arrive
+          ptx::mbar_wait(bar(bPVDone + g), (j - 1) & 1);
+          ptx::tc_fence_after();
           const float alpha = (m_new == -INFINITY) ? 1.0f : fast_exp2(m_ref - m_new);   // m_ref=-inf -> 0
           l_run *= alpha;
 #pragma unroll
@@ -202,41 +241,32 @@ attn_sm100_kernel(const AttnParams p, const __grid_constant__ TmaMaps maps) {
         }
         m_ref = m_new;
       }
-      const float m_use = (m_ref == -INFINITY) ? 0.f : m_ref;
-      float sum = 0.f;
+      const float neg_m = (m_ref == -INFINITY) ? 0.f : -m_ref;
+      float s0 = 0.f, s1 = 0.f, s2 = 0.f, s3 = 0.f;
+      uint32_t pk[kBN / 2];
 #pragma unroll
-      for (int e = 0; e < BN; ++e) {
-        x[e] = fast_exp2(x[e] - m_use);
-        sum += x[e];
+      for (int e = 0; e < kBN; e += 4) {
+        float q0 = fmaf(x[e], sc, neg_m), q1 = fmaf(x[e + 1], sc, neg_m);
+        float q2 = fmaf(x[e + 2], sc, neg_m), q3 = fmaf(x[e + 3], sc, neg_m);
+        q0 = ((e & 7) + 0 < kEmu) ? exp2_poly(q0) : fast_exp2(q0);
+        q1 = ((e & 7) + 1 < kEmu) ? exp2_poly(q1) : fast_exp2(q1);
+        q2 = ((e & 7) + 2 < kEmu) ? exp2_poly(q2) : fast_exp2(q2);
+        q3 = ((e & 7) + 3 < kEmu) ? exp2_poly(q3) : fast_exp2(q3);
+        s0 += q0; s1 += q1; s2 += q2; s3 += q3;
+        pk[e / 2] = pack2(q0, q1);
+        pk[e / 2 + 1] = pack2(q2, q3);
       }
-      l_run += sum;
-      if (kPTmem) {
-#pragma unroll
-        for (int c = 0; c < BN / 64; ++c) {
-          uint32_t r[32];
-#pragma unroll
-          for (int e = 0; e < 32; ++e) r[e] = pack2(x[c * 64 + 2 * e], x[c * 64 + 2 * e + 1]);
-          ptx::tmem_st32(tS + c * 32, r);
-        }
-        ptx::tc_wait_st();
-      } else {
-        // K-major, 128B swizzle: row r of a 64-key panel = 128 B; 16-byte chunk c lands at c ^ (r & 7)
-        const uint32_t prow = sP + g * (C::kPBytes / 2) + (row_in_tile >> 3) * 1024 + (row_in_tile & 7) * 128;
-#pragma unroll
-        for (int c = 0; c < BN / 8; ++c) {
-          const uint32_t addr = prow + (c >> 3) * (kBM * 128) + (((c & 7) ^ (row_in_tile & 7)) << 4);
-          asm volatile("st.shared.v4.b32 [%0], {%1,%2,%3,%4};" ::"r"(addr),
-                       "r"(pack2(x[c * 8 + 0], x[c * 8 + 1])), "r"(pack2(x[c * 8 + 2], x[c * 8 + 3])),
-                       "r"(pack2(x[c * 8 + 4], x[c * 8 + 5])), "r"(pack2(x[c * 8 + 6], x[c * 8 + 7])) : "memory");
-        }
-        ptx::fence_proxy_async();
-      }
+      l_run += (s0 + s1) + (s2 + s3);
+      ptx::tmem_st32(tS, pk);
+      ptx::tc_wait_st();
       ptx::tc_fence_before();
-      ptx::mbar_arrive(bar(B::p_ready + g));
+      __syncwarp();
+      if (lane == 0) ptx::mbar_arrive(bar(bPReady + g * 2 + buf));
     }
 
     // ---- epilogue: O / l -> bf16 -> global ------------------------------------
-    ptx::mbar_wait(bar(B::o_full + g), 0);
+    // (a parity wait on bPVDone could pass one completion early here: PV(total-2) may still be in flight)
+    ptx::mbar_wait(bar(bOFull + g), 0);
     ptx::tc_fence_after();
     const float inv = l_run > 0.f ? fast_rcp(l_run) : 0.f;
     __nv_bfloat16* orow = p.out + (long long)(seq_start + i) * p.o_stride + head * kD;
