@@ -34,7 +34,7 @@ int sm100_variant() {
   static int v = -1;
   if (v < 0) {
     const char* e = std::getenv("TMX_SM100_VARIANT");
-    v = e ? (std::atoi(e) & 3) : 0;
+    v = e ? (std::atoi(e) & 15) : 0;
   }
   return v;
 }

@@ -113,22 +113,22 @@ int sm100_block_n(int) { return kBN; }
 int launch_attn_sm100(const AttnParams& p, int variant, cudaStream_t s) {
   if ((p.Hq / p.Hkv) % 2 != 0) return TMX_ERR_UNSUPPORTED;   // needs two query heads per KV head
   if (!(p.scale_log2 > 0.f)) return TMX_ERR_UNSUPPORTED;     // row max is taken on raw scores
-  static bool attr_set = false;
-  if (!attr_set) {
-    TMX_CUDA_TRY(cudaFuncSetAttribute(attn_sm100_kernel<0>, cudaFuncAttributeMaxDynamicSharedMemorySize, kSmem));
-    TMX_CUDA_TRY(cudaFuncSetAttribute(attn_sm100_kernel<2>, cudaFuncAttributeMaxDynamicSharedMemorySize, kSmem));
-    attr_set = true;
-  }
+  const int emu = variant & 1, dbg = (variant >> 1) & 3, ping = (variant >> 3) & 1;   // TMX_SM100_VARIANT bits
+  void (*kern)(const AttnParams, const TmaMaps) = attn_sm100_kernel<0>;
+  if (dbg == 1) kern = attn_sm100_kernel<0, 1>;
+  else if (dbg == 3) kern = attn_sm100_kernel<0, 3>;
+  else if (dbg == 2) kern = ping ? (emu ? attn_sm100_kernel<2, 2, true> : attn_sm100_kernel<0, 2, true>)
+                                 : (emu ? attn_sm100_kernel<2, 2> : attn_sm100_kernel<0, 2>);
+  else kern = ping ? (emu ? attn_sm100_kernel<2, 0, true> : attn_sm100_kernel<0, 0, true>)
+                   : (emu ? attn_sm100_kernel<2> : attn_sm100_kernel<0>);
+  TMX_CUDA_TRY(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, kSmem));
   TmaMaps maps;
   int st = make_map(&maps.q, p.q, p.total_T, (long long)p.Hq * kD, p.q_stride, kBM);
   if (st == TMX_OK) st = make_map(&maps.k, p.k, p.total_T, (long long)p.Hkv * kD, p.kv_stride, kBN);
   if (st == TMX_OK) st = make_map(&maps.v, p.v, p.total_T, (long long)p.Hkv * kD, p.kv_stride, kBN);
   if (st != TMX_OK) return st;
   dim3 grid((unsigned)p.n_slots, (unsigned)(p.Hq / 2));
-  if (variant & 1)   // a quarter of the exponentials on the FMA pipe
-    attn_sm100_kernel<2><<<grid, kThreads, kSmem, s>>>(p, maps);
-  else
-    attn_sm100_kernel<0><<<grid, kThreads, kSmem, s>>>(p, maps);
+  kern<<<grid, kThreads, kSmem, s>>>(p, maps);
   count_launch();
   TMX_CUDA_TRY(cudaGetLastError());
   return TMX_OK;

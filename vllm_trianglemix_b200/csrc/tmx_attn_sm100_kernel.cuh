@@ -17,7 +17,11 @@ __device__ __forceinline__ float exp2_poly(float t) {
   return __int_as_float(__float_as_int(pl) + (__float_as_int(r) << 23));
 }
 
-template <int kEmu>
+// kDbg (developer timing experiments, results are garbage): 1 = MMA/TMA side alone (no softmax,
+// no waits for P), 2 = softmax side alone (S tiles 0/1 computed once and re-read).
+// kDbg 3 = as 1, but S issued as N=128 MMAs every other tile (timing of the MMA shape only).
+// kPing: the two softmax warps that share an SM sub-partition take turns in their exp phase.
+template <int kEmu, int kDbg = 0, bool kPing = false>
 __global__ void __launch_bounds__(kThreads, 1)
 attn_sm100_kernel(const AttnParams p, const __grid_constant__ TmaMaps maps) {
   extern __shared__ uint8_t smem_raw[];
@@ -92,7 +96,7 @@ attn_sm100_kernel(const AttnParams p, const __grid_constant__ TmaMaps maps) {
       };
       load_k(0);
       if (total > 1) load_k(1);
-      for (int it = 0; it < total; ++it) {
+      for (int it = 0; it < total && kDbg != 2; ++it) {
         load_v(it);
         if (it + 2 < total) load_k(it + 2);
       }
@@ -145,20 +149,33 @@ attn_sm100_kernel(const AttnParams p, const __grid_constant__ TmaMaps maps) {
       __syncwarp();
     }
     int vst = 0, vph = 0, kst = 2 % kKStages, kph = 0;     // stage / parity of V(j) and K(j+2)
-    for (int j = 0; j < ntot; ++j) {
+    if (kDbg == 2 && ptx::elect_one()) { ptx::mma_commit(bar(bOFull + 0)); ptx::mma_commit(bar(bOFull + 1)); }
+    constexpr uint32_t kIdescS128 = ptx::instr_desc_bf16(128, 128, false);
+    for (int j = 0; j < ntot && kDbg != 2; ++j) {
       const int buf = j & 1, pph = (j >> 1) & 1;
       const bool more = j + 2 < ntot;
       ptx::mbar_wait(bar(bVFull + vst), vph);
 #pragma unroll
       for (int g = 0; g < 2; ++g) {
-        ptx::mbar_wait(bar(bPReady + g * 2 + buf), pph);
+        if (kDbg != 1 && kDbg != 3) ptx::mbar_wait(bar(bPReady + g * 2 + buf), pph);
         if (more && g == 0) ptx::mbar_wait(bar(bKFull + kst), kph);
         ptx::tc_fence_after();
         if (ptx::elect_one()) {
           issue_pv(g, buf, vst, j > 0);
           ptx::mma_commit(bar(j + 1 < ntot ? bPVDone + g : bOFull + g));
           if (g == 1) ptx::mma_commit(bar(bVEmpty + vst));
-          if (more) {
+          if (more && kDbg == 3) {
+            if (buf == 0) {
+              const uint32_t d_tmem = tb + kColS + (uint32_t)(g * 128);
+              const uint64_t qa = dQ + (uint64_t)((g * 2 * (kBM * 128)) >> 4);
+#pragma unroll
+              for (int ks = 0; ks < 8; ++ks)
+                ptx::mma_ss(d_tmem, qa + (uint64_t)(((ks >> 2) * (kBM * 128) + (ks & 3) * 32) >> 4),
+                            dK + (uint64_t)(((ks >> 2) * kPanelBytes + (ks & 3) * 32) >> 4), kIdescS128, ks > 0);
+            }
+            ptx::mma_commit(bar(bSFull + g * 2 + buf));
+            if (g == 1) ptx::mma_commit(bar(bKEmpty + kst));
+          } else if (more) {
             issue_s(g, buf, kst);
             ptx::mma_commit(bar(bSFull + g * 2 + buf));
             if (g == 1) ptx::mma_commit(bar(bKEmpty + kst));
@@ -182,10 +199,12 @@ attn_sm100_kernel(const AttnParams p, const __grid_constant__ TmaMaps maps) {
     float m_ref = -INFINITY, l_run = 0.f;          // running max (scaled, log2 domain) and row sum
     const uint32_t* bm_row = p.bitmask ? p.bitmask + (long long)min(i, n - 1) * p.bitmask_stride : nullptr;
 
-    for (int j = 0; j < total; ++j) {
+    const int tok_mine = 1 + (warp & 3) * 2 + g, tok_other = 1 + (warp & 3) * 2 + (g ^ 1);
+    if (kPing && g == 1) ptx::named_arrive(tok_other, 64);      // group A goes first
+    for (int j = 0; j < total && kDbg != 1 && kDbg != 3; ++j) {
       const int buf = j & 1;
       const uint32_t tS = tSg + (uint32_t)(buf * 64);
-      ptx::mbar_wait(bar(bSFull + g * 2 + buf), (j >> 1) & 1);
+      ptx::mbar_wait(bar(bSFull + g * 2 + buf), kDbg == 2 ? 0 : (j >> 1) & 1);
       ptx::tc_fence_after();
       uint32_t xr[kBN];
       ptx::tmem_ld32(tS, *reinterpret_cast<uint32_t(*)[32]>(&xr[0]));
@@ -224,7 +243,7 @@ attn_sm100_kernel(const AttnParams p, const __grid_constant__ TmaMaps maps) {
       if (__any_sync(0xffffffffu, grow)) {
         if (j > 0) {
           // O holds tiles 0..j-1 once PV(j-1) has completed; PV(j) cannot start before our arrive
-          ptx::mbar_wait(bar(bPVDone + g), (j - 1) & 1);
+          if (kDbg != 2) ptx::mbar_wait(bar(bPVDone + g), (j - 1) & 1);
           ptx::tc_fence_after();
           const float alpha = (m_new == -INFINITY) ? 1.0f : fast_exp2(m_ref - m_new);   // m_ref=-inf -> 0
           l_run *= alpha;
@@ -242,6 +261,7 @@ attn_sm100_kernel(const AttnParams p, const __grid_constant__ TmaMaps maps) {
         m_ref = m_new;
       }
       const float neg_m = (m_ref == -INFINITY) ? 0.f : -m_ref;
+      if (kPing) ptx::named_sync(tok_mine, 64);
       float s0 = 0.f, s1 = 0.f, s2 = 0.f, s3 = 0.f;
       uint32_t pk[kBN / 2];
 #pragma unroll
@@ -257,11 +277,12 @@ attn_sm100_kernel(const AttnParams p, const __grid_constant__ TmaMaps maps) {
         pk[e / 2 + 1] = pack2(q2, q3);
       }
       l_run += (s0 + s1) + (s2 + s3);
+      if (kPing) ptx::named_arrive(tok_other, 64);
       ptx::tmem_st32(tS, pk);
       ptx::tc_wait_st();
       ptx::tc_fence_before();
       __syncwarp();
-      if (lane == 0) ptx::mbar_arrive(bar(bPReady + g * 2 + buf));
+      if (lane == 0 && kDbg != 2) ptx::mbar_arrive(bar(bPReady + g * 2 + buf));
     }
 
     // ---- epilogue: O / l -> bf16 -> global ------------------------------------
