@@ -1,0 +1,89 @@
+"""Head-sharded partition of the TriangleMix prefill path across the GPUs of one box.
+
+Heads never interact inside attention, so rank r of P owns KV heads
+[r*Hkv/P, (r+1)*Hkv/P) and the Hq/Hkv query heads of each -- the split the
+reference computes per tensor-parallel rank (vllm/model_executor/models/qwen3.py:85-98:
+``num_heads = total/tp``, ``num_kv_heads = max(1, total_kv/tp)``).  The block index is
+head-independent and rebuilt per rank; the only collective on the path is one
+all-gather of the [T, Hq/P, D] output shard (the analogue of ``gather_output`` in the
+reference's column-parallel layers, vllm/model_executor/layers/linear.py:559).
+
+Host logic only (works with any torch.distributed backend; the CPU tests use gloo).
+"""
+from __future__ import annotations
+
+from dataclasses import dataclass
+from typing import Optional
+
+import torch
+import torch.distributed as dist
+
+
+@dataclass(frozen=True)
+class HeadPartition:
+    rank: int
+    world: int
+    num_heads: int          # query heads on this rank
+    num_kv_heads: int       # KV heads on this rank
+    q_head_start: int       # first global query head owned
+    kv_head_start: int      # first global KV head owned
+    kv_replicas: int        # ranks sharing one KV head (1 unless world > total_kv_heads)
+
+    @property
+    def q_slice(self) -> slice:
+        return slice(self.q_head_start, self.q_head_start + self.num_heads)
+
+    @property
+    def kv_slice(self) -> slice:
+        return slice(self.kv_head_start, self.kv_head_start + self.num_kv_heads)
+
+
+def head_partition(rank: int, world: int, total_num_heads: int, total_num_kv_heads: int) -> HeadPartition:
+    """Per-rank head counts exactly as reference qwen3.py:85-98 computes them.
+
+    world <= total_kv_heads: KV heads are partitioned (world must divide them);
+    world >  total_kv_heads: KV heads are replicated (total_kv_heads must divide world),
+    each rank keeping one KV head and total_num_heads/world query heads of it.
+    """
+    if not (0 <= rank < world):
+        raise ValueError("rank %d outside world of %d" % (rank, world))
+    if total_num_heads % world != 0:
+        raise ValueError("total_num_heads %d not divisible by world %d" % (total_num_heads, world))
+    if total_num_heads % total_num_kv_heads != 0:
+        raise ValueError("query heads %d not a multiple of KV heads %d" % (total_num_heads, total_num_kv_heads))
+    hq = total_num_heads // world
+    if total_num_kv_heads >= world:
+        if total_num_kv_heads % world != 0:
+            raise ValueError("total_num_kv_heads %d not divisible by world %d" % (total_num_kv_heads, world))
+        hkv, rep = total_num_kv_heads // world, 1
+        kv_start = rank * hkv
+    else:
+        if world % total_num_kv_heads != 0:
+            raise ValueError("world %d not a multiple of total_num_kv_heads %d" % (world, total_num_kv_heads))
+        hkv, rep = 1, world // total_num_kv_heads
+        kv_start = rank // rep
+    return HeadPartition(rank, world, hq, hkv, rank * hq, kv_start, rep)
+
+
+def shard_heads(x: torch.Tensor, part: HeadPartition, kind: str) -> torch.Tensor:
+    """Slice a global [T, H, D] tensor down to this rank's heads (kind = 'q' or 'kv')."""
+    sl = part.q_slice if kind == "q" else part.kv_slice
+    return x[:, sl, :]
+
+
+def all_gather_heads(out_shard: torch.Tensor, gathered: Optional[torch.Tensor] = None, group=None,
+                     async_op: bool = False):
+    """All-gather [T, Hq/P, D] output shards into [P, T, Hq/P, D] (rank-major, one contiguous
+    message per rank: what ncclAllGather produces).  Returns (gathered, work_or_None)."""
+    world = dist.get_world_size(group)
+    shard = out_shard.contiguous()
+    if gathered is None:
+        gathered = torch.empty((world,) + tuple(shard.shape), dtype=shard.dtype, device=shard.device)
+    work = dist.all_gather_into_tensor(gathered.view(-1), shard.view(-1), group=group, async_op=async_op)
+    return gathered, work
+
+
+def heads_from_gathered(gathered: torch.Tensor) -> torch.Tensor:
+    """[P, T, Hq/P, D] -> the global [T, Hq, D] view order (a permuted view, no copy)."""
+    p, t, h, d = gathered.shape
+    return gathered.permute(1, 0, 2, 3).reshape(t, p * h, d)
