@@ -34,7 +34,7 @@ int sm100_variant() {
   static int v = -1;
   if (v < 0) {
     const char* e = std::getenv("TMX_SM100_VARIANT");
-    v = e ? (std::atoi(e) & 15) : 0;
+    v = e ? (std::atoi(e) & 255) : 0;
   }
   return v;
 }
@@ -170,6 +170,9 @@ extern "C" int tmx_prefill_attn(void* out, const void* q, const void* k, const v
   st = build_slots(reinterpret_cast<SlotInfo*>(ws + pl.off_slots), pl.n_slots, cu_seqlens, B,
                    max_seqlen, pl.bm, pl.bn, si, sl, last, mode, s);
   if (st != TMX_OK) return st;
-  if (pl.kernel == TMX_KERNEL_TCGEN05) return launch_attn_sm100(p, sm100_variant(), s);
+  if (pl.kernel == TMX_KERNEL_TCGEN05) {
+    const int var = sm100_variant();
+    return sm100_use_v2(var) ? launch_attn_sm100(p, var & 15, s) : launch_attn_sm100_v3(p, var & 15, s);
+  }
   return launch_attn_mma(p, pl.bm, s);
 }

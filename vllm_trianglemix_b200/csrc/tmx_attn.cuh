@@ -26,8 +26,12 @@ struct AttnParams {
 int build_slots(SlotInfo* slots, int n_slots, const int* cu, int B, int max_seqlen, int bm, int bn,
                 int si, int sl, int last, int mode, cudaStream_t s);
 int launch_attn_mma(const AttnParams& p, int bm, cudaStream_t s);
-int launch_attn_sm100(const AttnParams& p, int variant, cudaStream_t s);
-int sm100_block_n(int variant);
-int sm100_variant();   // TMX_SM100_VARIANT env (developer switch), default 0
+int launch_attn_sm100(const AttnParams& p, int variant, cudaStream_t s);      // 64-key tiles (v2)
+int launch_attn_sm100_v3(const AttnParams& p, int variant, cudaStream_t s);   // 128-key tiles (v3, default)
+// TMX_SM100_VARIANT env (developer switch), default 0: bit 7 selects the 64-key kernel, the low
+// bits are that kernel's own timing/emulation switches.
+int sm100_variant();
+inline bool sm100_use_v2(int variant) { return (variant & 128) != 0; }
+inline int sm100_block_n(int variant) { return sm100_use_v2(variant) ? 64 : 128; }
 
 }  // namespace tmx

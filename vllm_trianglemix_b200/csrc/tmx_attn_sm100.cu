@@ -108,8 +108,6 @@ int make_map(CUtensorMap* m, const void* base, long long rows, long long cols, l
 
 }  // namespace
 
-int sm100_block_n(int) { return kBN; }
-
 int launch_attn_sm100(const AttnParams& p, int variant, cudaStream_t s) {
   if ((p.Hq / p.Hkv) % 2 != 0) return TMX_ERR_UNSUPPORTED;   // needs two query heads per KV head
   if (!(p.scale_log2 > 0.f)) return TMX_ERR_UNSUPPORTED;     // row max is taken on raw scores

@@ -1,0 +1,443 @@
+// Masked GQA prefill attention on the 5th-generation tensor cores, 128-key tiles (kernel v3).
+//
+// One CTA = one 128-token query tile x TWO query heads that share a KV head (GQA reuse:
+// every K/V tile is fetched once for 256 query rows).  10 warps:
+//   warps 0-3  softmax group A (head h0):   one thread per query row, TMEM lanes 0..127
+//   warps 4-7  softmax group B (head h0+1)
+//   warp  8    TMA producer: Q once, then K(0) V(0) K(1) V(1) ... of the tiles the block index
+//              lists, through ONE ring of 5 x 32 KB stages (consumption order = load order)
+//   warp  9    MMA issuer (warp-uniform loop, one elected lane issues tcgen05.mma)
+// KV tiles are 128 keys, so both contractions run as M128 N128 MMAs (the shape that reaches
+// the tensor-pipe peak; the 64-key kernel's N=64 score MMAs top out ~15 % lower).
+// TMEM (512 columns): S_A | S_B (128 fp32 columns each) | O_A | O_B (128 each).  bf16 P
+// overwrites columns [0,64) of the S buffer it came from and is read by the MMA from TMEM.
+// Issue order   S_A(0) S_B(0) { PV_A(j) S_A(j+1) PV_B(j) S_B(j+1) }_j :
+// while one group exponentiates, the tensor pipe runs the other group's PV and next scores.
+// "S_g(j+1) complete" implies "PV_g(j) complete" (commit order), so a group may rescale its
+// O accumulator in TMEM right after it sees its next scores -- done lazily, only when some
+// row's running max grew by more than 2^8.  A share of the exponentials runs on the FMA pipe
+// (cubic 2^f, Cody-Waite split) because MUFU.EX2 at 16/clk/SM costs exactly as many cycles
+// per tile as the two MMAs.  Fully masked KV tiles are never loaded; only PARTIAL tiles
+// evaluate the mask predicate (or read the bitmask).
+//
+// Replaces vllm/attention/ascend_trianglemix.py:86-106 of the reference for dense-causal
+// layers (and for any triangle setting through the same block index).
+#include "tmx_attn.cuh"
+#include "tmx_sm100_ptx.cuh"
+#include "tmx_tma.cuh"
+
+namespace tmx {
+namespace {
+
+constexpr int kD = 128;
+constexpr int kBM = 128;
+constexpr int kBN = 128;
+constexpr int kThreads = 320;
+constexpr int kQBytes = 2 * 2 * kBM * 128;        // 2 heads x 2 panels of [128 rows][64 d] = 64 KB
+constexpr int kPanelBytes = kBN * 128;            // [128 keys][64 d] bf16 = 16 KB
+constexpr int kTileBytes = 2 * kPanelBytes;       // K or V tile = 32 KB
+constexpr int kStages = 5;
+constexpr int kOffRing = kQBytes;
+constexpr int kOffBar = kOffRing + kStages * kTileBytes;
+
+constexpr int bQFull = 0;
+constexpr int bFull = 1;                          // [kStages]
+constexpr int bEmpty = bFull + kStages;           // [kStages]
+constexpr int bSFull = bEmpty + kStages;          // [2 groups]
+constexpr int bPReady = bSFull + 2;               // [2 groups], 4 arrivals (one per warp)
+constexpr int bOFull = bPReady + 2;               // [2 groups]
+constexpr int kNumBars = bOFull + 2;
+constexpr int kSmem = kOffBar + kNumBars * 8 + 16 + 1024;   // + alignment slack
+static_assert(kSmem <= 232448, "exceeds the 227 KB of shared memory a CTA may use");
+
+constexpr uint32_t kColS = 0;      // + g * 128
+constexpr uint32_t kColO = 256;    // + g * 128
+
+__device__ __forceinline__ uint32_t pack2(float lo, float hi) {
+  __nv_bfloat162 v = __floats2bfloat162_rn(lo, hi);
+  return *reinterpret_cast<uint32_t*>(&v);
+}
+
+// 2^t on the FMA/ALU pipes (no MUFU): round-to-nearest split t = n + f, f in [-0.5, 0.5],
+// cubic minimax for 2^f (max rel. error 7.5e-5, far below bf16's 2^-9), n added into the
+// exponent field.  t is clamped at -126 (result then ~1e-38, i.e. 0 for bf16).
+__device__ __forceinline__ float exp2_poly(float t) {
+  t = fmaxf(t, -126.0f);
+  const float r = t + 12582912.0f;          // 1.5 * 2^23: low mantissa bits of r hold n
+  const float f = t - (r - 12582912.0f);
+  float pl = fmaf(0.0551716685f, f, 0.2426111251f);
+  pl = fmaf(pl, f, 0.6932609677f);
+  pl = fmaf(pl, f, 0.9999280572f);
+  return __int_as_float(__float_as_int(pl) + (__float_as_int(r) << 23));
+}
+
+// packed fp32 pairs (Blackwell FFMA2 / FADD2)
+__device__ __forceinline__ uint64_t pk_f2(float lo, float hi) {
+  uint64_t r;
+  asm("mov.b64 %0, {%1, %2};" : "=l"(r) : "f"(lo), "f"(hi));
+  return r;
+}
+__device__ __forceinline__ void upk_f2(uint64_t v, float& lo, float& hi) {
+  asm("mov.b64 {%0, %1}, %2;" : "=f"(lo), "=f"(hi) : "l"(v));
+}
+__device__ __forceinline__ uint64_t ffma2(uint64_t a, uint64_t b, uint64_t c) {
+  uint64_t d;
+  asm("fma.rn.f32x2 %0, %1, %2, %3;" : "=l"(d) : "l"(a), "l"(b), "l"(c));
+  return d;
+}
+__device__ __forceinline__ uint64_t fadd2(uint64_t a, uint64_t b) {
+  uint64_t d;
+  asm("add.rn.f32x2 %0, %1, %2;" : "=l"(d) : "l"(a), "l"(b));
+  return d;
+}
+// exp2_poly on a pair
+__device__ __forceinline__ uint64_t exp2_poly2(uint64_t t2) {
+  float t0, t1;
+  upk_f2(t2, t0, t1);
+  t2 = pk_f2(fmaxf(t0, -126.0f), fmaxf(t1, -126.0f));
+  const uint64_t magic = pk_f2(12582912.0f, 12582912.0f), nmagic = pk_f2(-12582912.0f, -12582912.0f);
+  const uint64_t r2 = fadd2(t2, magic);
+  const uint64_t u2 = fadd2(r2, nmagic);
+  const uint64_t f2 = ffma2(u2, pk_f2(-1.0f, -1.0f), t2);
+  uint64_t pl = ffma2(pk_f2(0.0551716685f, 0.0551716685f), f2, pk_f2(0.2426111251f, 0.2426111251f));
+  pl = ffma2(pl, f2, pk_f2(0.6932609677f, 0.6932609677f));
+  pl = ffma2(pl, f2, pk_f2(0.9999280572f, 0.9999280572f));
+  float p0, p1, r0, r1;
+  upk_f2(pl, p0, p1);
+  upk_f2(r2, r0, r1);
+  p0 = __int_as_float(__float_as_int(p0) + (__float_as_int(r0) << 23));
+  p1 = __int_as_float(__float_as_int(p1) + (__float_as_int(r1) << 23));
+  return pk_f2(p0, p1);
+}
+
+// kEmu: how many of every 16 exponentials run on the FMA pipe (even: 0, 4, 6, 8).
+// kDbg (developer timing experiments, results are garbage): 1 = MMA/TMA side alone,
+// 2 = softmax side alone (S tile 0 computed once and re-read), 3 = group A alone (serial chain).
+template <int kEmu, int kDbg>
+__global__ void __launch_bounds__(kThreads, 1)
+attn_sm100_v3_kernel(const AttnParams p, const __grid_constant__ TmaMaps maps) {
+  extern __shared__ uint8_t smem_raw[];
+  const uint32_t smem_base = (ptx::smem_u32(smem_raw) + 1023u) & ~1023u;   // SWIZZLE_128B: 1024-byte atoms
+  const uint32_t sQ = smem_base, sRing = smem_base + kOffRing;
+  const uint32_t sBar = smem_base + kOffBar;
+  const uint32_t sTmemPtr = sBar + kNumBars * 8;
+  auto bar = [&](int i) { return sBar + 8u * (uint32_t)i; };
+
+  const int warp = __shfl_sync(0xffffffffu, (int)(threadIdx.x >> 5), 0);   // provably warp-uniform
+  const int lane = threadIdx.x & 31;
+
+  // ---- work item (uniform per CTA) -------------------------------------------
+  const SlotInfo slot = p.slots[p.n_slots - 1 - blockIdx.x];      // descending: longest first
+  if (slot.seq < 0) return;
+  const int n = slot.n, r0 = slot.q_tile * kBM;
+  const int r1 = min(n, r0 + kBM) - 1;
+  const int lo0 = slot.lo0, cnt0 = slot.hi0 - slot.lo0, lo1 = slot.lo1;
+  const int total = cnt0 + (slot.hi1 - slot.lo1);
+  const int seq_start = p.cu[slot.seq];
+  const int h0 = 2 * blockIdx.y;
+  const int kvh = h0 / (p.Hq / p.Hkv);
+  const int lrow = first_dense_row(n, p.last);
+  auto tile_of = [&](int it) { return it < cnt0 ? lo0 + it : lo1 + (it - cnt0); };
+
+  // ---- setup -------------------------------------------------------------------
+  if (warp == 8 && lane == 0) {
+    ptx::prefetch_tmap(&maps.q); ptx::prefetch_tmap(&maps.k); ptx::prefetch_tmap(&maps.v);
+    ptx::mbar_init(bar(bQFull), 1);
+    for (int s = 0; s < kStages; ++s) { ptx::mbar_init(bar(bFull + s), 1); ptx::mbar_init(bar(bEmpty + s), 1); }
+    for (int g = 0; g < 2; ++g) {
+      ptx::mbar_init(bar(bSFull + g), 1);
+      ptx::mbar_init(bar(bPReady + g), 4);       // one arrive per softmax warp of the group
+      ptx::mbar_init(bar(bOFull + g), 1);
+    }
+    ptx::fence_barrier_init();
+  }
+  if (warp == 9) ptx::tmem_alloc(sTmemPtr, 512);
+  ptx::tc_fence_before();
+  __syncthreads();
+  ptx::tc_fence_after();
+  uint32_t tmem_base;
+  asm volatile("ld.shared.b32 %0, [%1];" : "=r"(tmem_base) : "r"(sTmemPtr));
+
+  if (warp == 8) {
+    // =========================== TMA producer ===========================
+    if (ptx::elect_one()) {
+      ptx::mbar_expect_tx(bar(bQFull), kQBytes);
+      for (int g = 0; g < 2; ++g)
+        for (int pnl = 0; pnl < 2; ++pnl)
+          ptx::tma_load_2d(sQ + (g * 2 + pnl) * (kBM * 128), &maps.q, bar(bQFull),
+                           (h0 + g) * kD + pnl * 64, seq_start + r0);
+      const int items = (kDbg == 2) ? 1 : 2 * total;     // item t: even = K(t/2), odd = V(t/2)
+      int st = 0;
+      for (int t = 0; t < items; ++t) {
+        if (t >= kStages) ptx::mbar_wait(bar(bEmpty + st), ((t / kStages) - 1) & 1);
+        ptx::mbar_expect_tx(bar(bFull + st), kTileBytes);
+        const int row = seq_start + tile_of(t >> 1) * kBN;
+        const CUtensorMap* m = (t & 1) ? &maps.v : &maps.k;
+        for (int pnl = 0; pnl < 2; ++pnl)
+          ptx::tma_load_2d(sRing + st * kTileBytes + pnl * kPanelBytes, m, bar(bFull + st),
+                           kvh * kD + pnl * 64, row);
+        if (++st == kStages) st = 0;
+      }
+    }
+    __syncwarp();
+  } else if (warp == 9) {
+    // =========================== MMA issuer ===========================
+    const uint32_t tb = __shfl_sync(0xffffffffu, tmem_base, 0);
+    const int ntot = __shfl_sync(0xffffffffu, total, 0);
+    constexpr uint32_t kIdescS = ptx::instr_desc_bf16(128, kBN, false);
+    constexpr uint32_t kIdescO = ptx::instr_desc_bf16(128, 128, true);
+    const uint64_t dQ = ptx::smem_desc(sQ, 16, 1024);
+    const uint64_t dK = ptx::smem_desc(sRing, 16, 1024);             // K tiles: K-major (d contiguous)
+    const uint64_t dV = ptx::smem_desc(sRing, kPanelBytes, 1024);    // V tiles: MN-major, LBO = d-panel pitch
+
+    // S_g = Q_g K^T of the tile in ring stage `st`: 8 k-steps of 16 over d (two 64-d panels)
+    auto issue_s = [&](int g, int st) {
+      const uint32_t d_tmem = tb + kColS + (uint32_t)(g * 128);
+      const uint64_t qa = dQ + (uint64_t)((g * 2 * (kBM * 128)) >> 4);
+      const uint64_t kb = dK + (uint64_t)((st * kTileBytes) >> 4);
+#pragma unroll
+      for (int ks = 0; ks < 8; ++ks) {
+        const uint32_t qo = ((ks >> 2) * (kBM * 128) + (ks & 3) * 32) >> 4;
+        const uint32_t ko = ((ks >> 2) * kPanelBytes + (ks & 3) * 32) >> 4;
+        ptx::mma_ss(d_tmem, qa + qo, kb + ko, kIdescS, ks > 0);
+      }
+    };
+    // O_g += P_g V: 8 k-steps of 16 keys; P (bf16) read from columns [0,64) of S_g
+    auto issue_pv = [&](int g, int st, bool acc) {
+      const uint32_t d_tmem = tb + kColO + (uint32_t)(g * 128);
+      const uint32_t a_tmem = tb + kColS + (uint32_t)(g * 128);
+      const uint64_t vb = dV + (uint64_t)((st * kTileBytes) >> 4);
+#pragma unroll
+      for (int ks = 0; ks < kBN / 16; ++ks)
+        ptx::mma_ts(d_tmem, a_tmem + (uint32_t)(ks * 8), vb + (uint64_t)((ks * 2048) >> 4), kIdescO,
+                    acc || ks > 0);
+    };
+
+    int st = 0, ph = 0;                               // ring position of the next item to consume
+    auto advance = [&] { if (++st == kStages) { st = 0; ph ^= 1; } };
+    ptx::mbar_wait(bar(bQFull), 0);
+    ptx::mbar_wait(bar(bFull + 0), 0);                // K(0)
+    ptx::tc_fence_after();
+    if (ptx::elect_one()) {
+      issue_s(0, 0); ptx::mma_commit(bar(bSFull + 0));
+      if (kDbg != 3) { issue_s(1, 0); ptx::mma_commit(bar(bSFull + 1)); }
+      if (kDbg != 2) ptx::mma_commit(bar(bEmpty + 0));
+      if (kDbg == 2) { ptx::mma_commit(bar(bOFull + 0)); ptx::mma_commit(bar(bOFull + 1)); }
+    }
+    __syncwarp();
+    advance();
+    for (int j = 0; j < ntot && kDbg != 2; ++j) {
+      const int vst = st, vph = ph;
+      advance();
+      const int kst = st, kph = ph;
+      const bool more = j + 1 < ntot;
+      if (more) advance();
+      ptx::mbar_wait(bar(bFull + vst), vph);
+#pragma unroll
+      for (int g = 0; g < 2; ++g) {
+        if (kDbg == 3 && g == 1) {       // one group alone: only release the ring stages
+          if (ptx::elect_one()) { ptx::mma_commit(bar(bEmpty + vst)); if (more) ptx::mma_commit(bar(bEmpty + kst)); }
+          __syncwarp();
+          continue;
+        }
+        if (kDbg != 1) ptx::mbar_wait(bar(bPReady + g), j & 1);
+        ptx::tc_fence_after();
+        if (ptx::elect_one()) {
+          issue_pv(g, vst, j > 0);
+          if (!more) ptx::mma_commit(bar(bOFull + g));
+          if (g == 1) ptx::mma_commit(bar(bEmpty + vst));
+        }
+        __syncwarp();
+        if (more) {
+          if (g == 0) { ptx::mbar_wait(bar(bFull + kst), kph); ptx::tc_fence_after(); }
+          if (ptx::elect_one()) {
+            issue_s(g, kst);
+            ptx::mma_commit(bar(bSFull + g));
+            if (g == 1) ptx::mma_commit(bar(bEmpty + kst));
+          }
+          __syncwarp();
+        }
+      }
+    }
+  } else {
+    // =========================== softmax groups ===========================
+    const int g = warp >> 2;                       // 0: head h0, 1: head h0 + 1
+    const int row_in_tile = (warp & 3) * 32 + lane;
+    const int i = r0 + row_in_tile;                // query row inside the sequence
+    const int head = h0 + g;
+    const uint32_t lane_base = (uint32_t)((warp & 3) * 32) << 16;
+    const uint32_t tS = tmem_base + lane_base + kColS + (uint32_t)(g * 128);
+    const uint32_t tO = tmem_base + lane_base + kColO + (uint32_t)(g * 128);
+    const float sc = p.scale_log2;                 // > 0 (checked by the launcher)
+    float m_ref = -INFINITY, l_run = 0.f;          // running max (scaled, log2 domain) and row sum
+    const uint32_t* bm_row = p.bitmask ? p.bitmask + (long long)min(i, n - 1) * p.bitmask_stride : nullptr;
+
+    const uint64_t sc2 = pk_f2(sc, sc);
+
+    for (int j = 0; j < total && kDbg != 1 && !(kDbg == 3 && g == 1); ++j) {
+      ptx::mbar_wait(bar(bSFull + g), kDbg == 2 ? 0 : (j & 1));
+      ptx::tc_fence_after();
+      const int c0 = tile_of(j) * kBN;
+      const bool full = bm_row == nullptr &&
+                        tile_is_full(r0, r1, c0, c0 + kBN - 1, n, lrow, p.si, p.sl, p.mode);
+      uint32_t pk[64];             // the row's 128 probabilities as bf16 pairs
+      float mx;                    // row max of the raw scores of this tile
+      uint64_t sum2;               // two partial row sums
+      // Optimistic single pass over S: exponentiate against the CURRENT reference max while
+      // tracking the tile's max.  Only if some row's max outgrew the reference by more than 2^8
+      // (always on the first tile, rarely afterwards) the reference is refreshed, O and l are
+      // rescaled and the pass is redone -- S is still intact in TMEM because P is stored last.
+#pragma unroll 1
+      for (int attempt = 0;; ++attempt) {
+        const float neg_m = (m_ref == -INFINITY) ? 0.f : -m_ref;
+        const uint64_t negm2 = pk_f2(neg_m, neg_m);
+        float mx0 = -INFINITY, mx1 = -INFINITY;
+        sum2 = pk_f2(0.f, 0.f);
+        // 32 scores (columns c0 + 32c ...) -> 16 packed bf16 pairs
+        auto chunk = [&](int c, uint32_t (&xr)[32]) {
+          float x[32];
+#pragma unroll
+          for (int e = 0; e < 32; ++e) x[e] = __uint_as_float(xr[e]);
+          if (!full) {
+            const int cb = c0 + c * 32;
+            if (bm_row == nullptr) {
+#pragma unroll
+              for (int e = 0; e < 32; ++e)
+                x[e] = attends(i, cb + e, n, lrow, p.si, p.sl, p.mode) ? x[e] : -INFINITY;
+            } else {
+              const uint32_t bits = bm_row[cb >> 5];
+#pragma unroll
+              for (int e = 0; e < 32; ++e) x[e] = ((bits >> e) & 1u) ? x[e] : -INFINITY;
+            }
+          }
+#pragma unroll
+          for (int e = 0; e < 32; e += 4) {
+            mx0 = fmaxf(mx0, fmaxf(x[e], x[e + 1]));
+            mx1 = fmaxf(mx1, fmaxf(x[e + 2], x[e + 3]));
+          }
+#pragma unroll
+          for (int e = 0; e < 32; e += 2) {
+            uint64_t q2 = ffma2(pk_f2(x[e], x[e + 1]), sc2, negm2);
+            float a, b;
+            if ((e & 15) < kEmu) {
+              q2 = exp2_poly2(q2);
+              upk_f2(q2, a, b);
+            } else {
+              upk_f2(q2, a, b);
+              a = fast_exp2(a);
+              b = fast_exp2(b);
+              q2 = pk_f2(a, b);
+            }
+            sum2 = fadd2(sum2, q2);
+            pk[c * 16 + e / 2] = pack2(a, b);
+          }
+        };
+        uint32_t xa[32], xb[32];
+        ptx::tmem_ld32(tS, xa);
+        ptx::tc_wait_ld();
+        ptx::tmem_ld32(tS + 32, xb);        // in flight while chunk 0 is processed
+        chunk(0, xa);
+        ptx::tc_wait_ld();
+        ptx::tmem_ld32(tS + 64, xa);
+        chunk(1, xb);
+        ptx::tc_wait_ld();
+        ptx::tmem_ld32(tS + 96, xb);
+        chunk(2, xa);
+        ptx::tc_wait_ld();
+        chunk(3, xb);
+        mx = fmaxf(mx0, mx1);
+        const float m_new = fmaxf(m_ref, mx * sc);
+        const bool grow = (m_new > m_ref + 8.0f) || (m_ref == -INFINITY && m_new > -INFINITY);
+        if (attempt == 1 || !__any_sync(0xffffffffu, grow)) break;
+        if (j > 0) {
+          // S(j) complete => PV(j-1) complete (commit order); PV(j) waits for our arrive below
+          const float alpha = (m_new == -INFINITY) ? 1.0f : fast_exp2(m_ref - m_new);   // m_ref=-inf -> 0
+          l_run *= alpha;
+#pragma unroll
+          for (int c = 0; c < 4; ++c) {
+            uint32_t r[32];
+            ptx::tmem_ld32(tO + c * 32, r);
+            ptx::tc_wait_ld();
+#pragma unroll
+            for (int e = 0; e < 32; ++e) r[e] = __float_as_uint(__uint_as_float(r[e]) * alpha);
+            ptx::tmem_st32(tO + c * 32, r);
+          }
+          ptx::tc_wait_st();
+        }
+        m_ref = m_new;
+      }
+      {
+        float a, b;
+        upk_f2(sum2, a, b);
+        l_run += a + b;
+      }
+      // bf16 P into columns [0,64) of S (every score of the tile has been read by now)
+      ptx::tmem_st32(tS, *reinterpret_cast<uint32_t(*)[32]>(&pk[0]));
+      ptx::tmem_st32(tS + 32, *reinterpret_cast<uint32_t(*)[32]>(&pk[32]));
+      ptx::tc_wait_st();
+      ptx::tc_fence_before();
+      __syncwarp();
+      if (lane == 0 && kDbg != 2) ptx::mbar_arrive(bar(bPReady + g));
+    }
+    // ---- epilogue: O / l -> bf16 -> global ------------------------------------
+    if (!(kDbg == 3 && g == 1)) ptx::mbar_wait(bar(bOFull + g), 0);
+    ptx::tc_fence_after();
+    const float inv = l_run > 0.f ? fast_rcp(l_run) : 0.f;
+    __nv_bfloat16* orow = p.out + (long long)(seq_start + i) * p.o_stride + head * kD;
+#pragma unroll
+    for (int c = 0; c < 4; ++c) {
+      uint32_t r[32];
+      ptx::tmem_ld32(tO + c * 32, r);
+      ptx::tc_wait_ld();
+      if (i <= r1) {
+#pragma unroll
+        for (int v4 = 0; v4 < 4; ++v4) {
+          uint4 o;
+          o.x = pack2(__uint_as_float(r[v4 * 8 + 0]) * inv, __uint_as_float(r[v4 * 8 + 1]) * inv);
+          o.y = pack2(__uint_as_float(r[v4 * 8 + 2]) * inv, __uint_as_float(r[v4 * 8 + 3]) * inv);
+          o.z = pack2(__uint_as_float(r[v4 * 8 + 4]) * inv, __uint_as_float(r[v4 * 8 + 5]) * inv);
+          o.w = pack2(__uint_as_float(r[v4 * 8 + 6]) * inv, __uint_as_float(r[v4 * 8 + 7]) * inv);
+          *reinterpret_cast<uint4*>(orow + c * 32 + v4 * 8) = o;
+        }
+      }
+    }
+    if (p.lse != nullptr && i <= r1)
+      p.lse[(long long)head * p.total_T + seq_start + i] = m_ref * 0.6931471805599453f + logf(l_run);
+    ptx::tc_fence_before();
+  }
+
+  // ---- teardown -------------------------------------------------------------------
+  __syncthreads();
+  if (warp == 9) {
+    ptx::tc_fence_after();
+    ptx::tmem_dealloc(tmem_base, 512);
+  }
+}
+
+}  // namespace
+
+int launch_attn_sm100_v3(const AttnParams& p, int variant, cudaStream_t s) {
+  if ((p.Hq / p.Hkv) % 2 != 0) return TMX_ERR_UNSUPPORTED;   // needs two query heads per KV head
+  if (!(p.scale_log2 > 0.f)) return TMX_ERR_UNSUPPORTED;     // row max is taken on raw scores
+  const int emu = variant & 3, dbg = (variant >> 2) & 3;     // TMX_SM100_VARIANT bits
+  using Kern = void (*)(const AttnParams, const TmaMaps);
+  static const Kern table[4][4] = {
+      {attn_sm100_v3_kernel<0, 0>, attn_sm100_v3_kernel<4, 0>, attn_sm100_v3_kernel<6, 0>, attn_sm100_v3_kernel<8, 0>},
+      {attn_sm100_v3_kernel<0, 1>, attn_sm100_v3_kernel<0, 1>, attn_sm100_v3_kernel<0, 1>, attn_sm100_v3_kernel<0, 1>},
+      {attn_sm100_v3_kernel<0, 2>, attn_sm100_v3_kernel<4, 2>, attn_sm100_v3_kernel<6, 2>, attn_sm100_v3_kernel<8, 2>},
+      {attn_sm100_v3_kernel<0, 3>, attn_sm100_v3_kernel<4, 3>, attn_sm100_v3_kernel<6, 3>, attn_sm100_v3_kernel<8, 3>}};
+  Kern kern = table[dbg][emu];
+  TMX_CUDA_TRY(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, kSmem));
+  TmaMaps maps;
+  int st = tma_map_2d(&maps.q, p.q, p.total_T, (long long)p.Hq * kD, p.q_stride, kBM);
+  if (st == TMX_OK) st = tma_map_2d(&maps.k, p.k, p.total_T, (long long)p.Hkv * kD, p.kv_stride, kBN);
+  if (st == TMX_OK) st = tma_map_2d(&maps.v, p.v, p.total_T, (long long)p.Hkv * kD, p.kv_stride, kBN);
+  if (st != TMX_OK) return st;
+  dim3 grid((unsigned)p.n_slots, (unsigned)(p.Hq / 2));
+  kern<<<grid, kThreads, kSmem, s>>>(p, maps);
+  count_launch();
+  TMX_CUDA_TRY(cudaGetLastError());
+  return TMX_OK;
+}
+
+}  // namespace tmx

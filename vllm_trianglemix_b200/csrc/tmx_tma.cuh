@@ -1,0 +1,47 @@
+// Host-side TMA descriptor helpers shared by the tcgen05 attention kernels.
+#pragma once
+#include <cuda.h>
+#include <cudaTypedefs.h>
+#include <mutex>
+#include "tmx_common.cuh"
+
+namespace tmx {
+
+struct TmaMaps {
+  CUtensorMap q, k, v;
+};
+
+inline PFN_cuTensorMapEncodeTiled_v12000 tma_encode_fn() {
+  static PFN_cuTensorMapEncodeTiled_v12000 fn = nullptr;
+  static std::once_flag once;
+  std::call_once(once, [] {
+    void* p = nullptr;
+    cudaDriverEntryPointQueryResult qres;
+    if (cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &p, cudaEnableDefault, &qres) == cudaSuccess &&
+        qres == cudaDriverEntryPointSuccess)
+      fn = reinterpret_cast<PFN_cuTensorMapEncodeTiled_v12000>(p);
+  });
+  return fn;
+}
+
+// [rows][cols] bf16 row-major with a row pitch of `pitch_elems`; box = 64 columns x box_rows,
+// 128-byte swizzle, out-of-bounds rows read as zero.
+inline int tma_map_2d(CUtensorMap* m, const void* base, long long rows, long long cols,
+                      long long pitch_elems, int box_rows) {
+  auto enc = tma_encode_fn();
+  if (!enc) return TMX_ERR_CUDA;
+  cuuint64_t dims[2] = {(cuuint64_t)cols, (cuuint64_t)rows};
+  cuuint64_t strides[1] = {(cuuint64_t)pitch_elems * 2};
+  cuuint32_t box[2] = {64u, (cuuint32_t)box_rows};
+  cuuint32_t estr[2] = {1u, 1u};
+  CUresult r = enc(m, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 2, const_cast<void*>(base), dims, strides, box, estr,
+                   CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B,
+                   CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+  if (r != CUDA_SUCCESS) {
+    set_cuda_error(cudaErrorInvalidValue, "cuTensorMapEncodeTiled");
+    return TMX_ERR_CUDA;
+  }
+  return TMX_OK;
+}
+
+}  // namespace tmx
