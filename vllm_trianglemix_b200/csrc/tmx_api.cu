@@ -59,14 +59,19 @@ size_t align_up(size_t x, size_t a) { return (x + a - 1) / a * a; }
 struct Plan {
   int kernel;      // TMX_KERNEL_MMA / TMX_KERNEL_TCGEN05
   int bm, bn;
+  int stream;      // triangle layer: streaming tcgen05 kernel + mma kernel on the tail tiles only
+  int stream_bm;   // tokens per streaming CTA
   int n_slots, last_tiles, nsplit_max;
   size_t off_slots, off_part_o, off_part_ml, total;
 };
 
-Plan make_plan(int B, int total_T, int max_seqlen, int Hq, int Hkv, int last, int mode, int kernel) {
+Plan make_plan(int B, int total_T, int max_seqlen, int Hq, int Hkv, int si, int sl, int last, int mode,
+               int kernel, bool allow_stream) {
   Plan pl{};
   // AUTO: the tcgen05 kernel serves every tensor-bound case it can pair heads for (dense-causal
-  // and unmasked layers); triangle layers (HBM-bound, split last tile) stay on the mma.sync kernel.
+  // and unmasked layers).  Triangle layers are HBM-bound: their sink + window part goes to the
+  // streaming tcgen05 kernel where it applies, the dense tail rows (and every other triangle
+  // setting) to the mma.sync kernel with split-KV.
   const bool pairable = Hkv > 0 && Hq % Hkv == 0 && (Hq / Hkv) % 2 == 0;
   pl.kernel = kernel;
   if (kernel == TMX_KERNEL_AUTO)
@@ -74,12 +79,16 @@ Plan make_plan(int B, int total_T, int max_seqlen, int Hq, int Hkv, int last, in
   pl.bn = 64;
   pl.bm = (mode == TMX_MODE_TRIANGLE) ? 64 : 128;
   if (pl.kernel == TMX_KERNEL_TCGEN05) { pl.bm = 128; pl.bn = sm100_block_n(sm100_variant()); }
-  pl.n_slots = total_T / pl.bm + B;
+  pl.stream = allow_stream && kernel == TMX_KERNEL_AUTO && mode == TMX_MODE_TRIANGLE &&
+              stream_supported(Hq, Hkv, si, sl) && (last <= 1 || last_tiles_max(last, pl.bm) > 0);
+  pl.stream_bm = pl.stream ? stream_block_m(Hq, Hkv) : 0;
+  pl.n_slots = total_T / (pl.stream ? pl.stream_bm : pl.bm) + B;
   pl.last_tiles = 0; pl.nsplit_max = 0;
   if (pl.kernel == TMX_KERNEL_MMA && mode == TMX_MODE_TRIANGLE) {
     int ns = nsplit_max(max_seqlen, pl.bn);
     int lt = last_tiles_max(last, pl.bm);
     if (lt > 0 && ceil_div(max_seqlen, pl.bn) >= kSplitMinTiles) { pl.last_tiles = lt; pl.nsplit_max = ns; }
+    else if (pl.stream) pl.last_tiles = lt;          // tail tiles without split workers
   }
   size_t off = 0;
   pl.off_slots = off; off = align_up(off + sizeof(SlotInfo) * (size_t)pl.n_slots, 256);
@@ -120,9 +129,12 @@ extern "C" int tmx_last_launch_count(void) { return g_launches; }
 
 extern "C" size_t tmx_attn_workspace_bytes(int B, int total_T, int max_seqlen, int Hq, int Hkv,
                                            int D, int si, int sl, int last, int mode, int kernel) {
-  (void)D; (void)si; (void)sl;
+  (void)D;
   if (B <= 0 || total_T <= 0) return 256;
-  return make_plan(B, total_T, max_seqlen, Hq, Hkv, last, mode, kernel).total;
+  // a bitmask (unknown here) disables the streaming plan: size for whichever plan is larger
+  const size_t a = make_plan(B, total_T, max_seqlen, Hq, Hkv, si, sl, last, mode, kernel, true).total;
+  const size_t b = make_plan(B, total_T, max_seqlen, Hq, Hkv, si, sl, last, mode, kernel, false).total;
+  return a > b ? a : b;
 }
 
 extern "C" int tmx_prefill_attn(void* out, const void* q, const void* k, const void* v,
@@ -149,7 +161,7 @@ extern "C" int tmx_prefill_attn(void* out, const void* q, const void* k, const v
   int st = check_arch();
   if (st != TMX_OK) return st;
 
-  Plan pl = make_plan(B, total_T, max_seqlen, Hq, Hkv, last, mode, kernel);
+  Plan pl = make_plan(B, total_T, max_seqlen, Hq, Hkv, si, sl, last, mode, kernel, bitmask == nullptr);
   if (!workspace || workspace_bytes < pl.total || mis(workspace)) return TMX_ERR_WORKSPACE;
   cudaStream_t s = (cudaStream_t)stream;
   uint8_t* ws = static_cast<uint8_t*>(workspace);
@@ -167,6 +179,18 @@ extern "C" int tmx_prefill_attn(void* out, const void* q, const void* k, const v
   p.si = si; p.sl = sl; p.last = last; p.mode = mode;
   p.scale_log2 = scale * 1.4426950408889634f;
 
+  if (pl.stream) {
+    // triangle layer = streaming kernel (rows before the first tail tile) + tail tiles
+    p.tail_bm = pl.bm;
+    st = build_slots(reinterpret_cast<SlotInfo*>(ws + pl.off_slots), pl.n_slots, cu_seqlens, B,
+                     max_seqlen, pl.stream_bm, pl.bn, si, sl, last, mode, s);
+    if (st != TMX_OK) return st;
+    st = launch_attn_stream(p, s);
+    if (st != TMX_OK || last <= 1 || pl.last_tiles == 0) return st;
+    p.tail_only = 1;
+    p.n_slots = B * pl.last_tiles;
+    return launch_attn_mma(p, pl.bm, s);
+  }
   st = build_slots(reinterpret_cast<SlotInfo*>(ws + pl.off_slots), pl.n_slots, cu_seqlens, B,
                    max_seqlen, pl.bm, pl.bn, si, sl, last, mode, s);
   if (st != TMX_OK) return st;

@@ -20,12 +20,18 @@ struct AttnParams {
   int B, total_T, max_seqlen, Hq, Hkv;
   int n_slots, last_tiles, nsplit_max;
   int si, sl, last, mode;
+  int tail_only;              // mma kernel: blockIdx.x < n_slots enumerates (sequence, tail tile) only
+  int tail_bm;                // stream kernel: query-tile size of the dense-tail path
   float scale_log2;           // scale * log2(e)
 };
 
 int build_slots(SlotInfo* slots, int n_slots, const int* cu, int B, int max_seqlen, int bm, int bn,
                 int si, int sl, int last, int mode, cudaStream_t s);
 int launch_attn_mma(const AttnParams& p, int bm, cudaStream_t s);
+// streaming part of triangle layers (tmx_attn_stream.cu)
+bool stream_supported(int Hq, int Hkv, int si, int sl);
+int stream_block_m(int Hq, int Hkv);
+int launch_attn_stream(const AttnParams& p, cudaStream_t s);
 int launch_attn_sm100(const AttnParams& p, int variant, cudaStream_t s);      // 64-key tiles (v2)
 int launch_attn_sm100_v3(const AttnParams& p, int variant, cudaStream_t s);   // 128-key tiles (v3, default)
 // TMX_SM100_VARIANT env (developer switch), default 0: bit 7 selects the 64-key kernel, the low

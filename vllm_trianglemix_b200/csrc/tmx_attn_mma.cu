@@ -85,7 +85,20 @@ __global__ void __launch_bounds__(BM * 2, (BM == 64 ? 3 : 1)) attn_mma_kernel(co
   const int head = blockIdx.y;
   const int kvh = head / (p.Hq / p.Hkv);
   int seq, n, r0, lo0, hi0, lo1, hi1, part = -1;
-  if ((int)blockIdx.x < p.n_slots) {
+  if ((int)blockIdx.x < p.n_slots && p.tail_only) {
+    // tail mode: only the query tiles holding dense tail rows (the streaming kernel owns the rest)
+    seq = blockIdx.x / p.last_tiles;
+    const int ql = blockIdx.x % p.last_tiles;
+    n = p.cu[seq + 1] - p.cu[seq];
+    const int lrow_ = first_dense_row(n, p.last);
+    if (n <= 0 || lrow_ >= n) return;
+    r0 = (lrow_ / BM + ql) * BM;
+    if (r0 >= n) return;
+    const int r1_ = min(n, r0 + BM) - 1;
+    if (split_count(r0, r1_, n, kBN, lrow_, p.last, p.mode, BM) > 0) return;   // split workers do it
+    const TileRanges t = touched_tiles(r0, r1_, n, kBN, lrow_, p.si, p.sl, p.mode);
+    lo0 = t.lo0; hi0 = t.hi0; lo1 = t.lo1; hi1 = t.hi1;
+  } else if ((int)blockIdx.x < p.n_slots) {
     const SlotInfo s = p.slots[p.n_slots - 1 - blockIdx.x];   // descending: longest first
     if (s.seq < 0 || s.nsplit > 0) return;
     seq = s.seq; n = s.n; r0 = s.q_tile * BM;
@@ -332,11 +345,14 @@ __global__ void __launch_bounds__(BM * 2, (BM == 64 ? 3 : 1)) attn_mma_kernel(co
   }
 }
 
-// Merge the split-KV partials of one (sequence, last tile, head): one thread per
-// (row, 4 columns).
+// Merge the split-KV partials of one (sequence, last tile, head): a CTA takes 8 rows, one thread
+// per (row, 4 columns); grid.x = B * last_tiles * BM / 8 so that the merge is a bandwidth-bound
+// pass over the partials instead of 64 serial CTAs.
 template <int BM>
 __global__ void __launch_bounds__(256) combine_kernel(const AttnParams p) {
-  int e = blockIdx.x;
+  constexpr int kRowsPerCta = 8;
+  int e = blockIdx.x / (BM / kRowsPerCta);
+  const int rblk = blockIdx.x % (BM / kRowsPerCta);
   int ql = e % p.last_tiles, seq = e / p.last_tiles;
   int head = blockIdx.y;
   int start = p.cu[seq], n = p.cu[seq + 1] - start;
@@ -349,28 +365,27 @@ __global__ void __launch_bounds__(256) combine_kernel(const AttnParams p) {
   int ns = split_count(r0, r1, n, kBN, lrow, p.last, p.mode, BM);
   if (ns == 0) return;
   long long base = (long long)(seq * p.last_tiles + ql) * p.nsplit_max;
-  for (int idx = threadIdx.x; idx < BM * 32; idx += blockDim.x) {
-    int r = idx >> 5, c4 = (idx & 31) * 4;
-    if (r0 + r > r1) continue;
-    float mmax = -INFINITY;
-    for (int s = 0; s < ns; ++s)
-      mmax = fmaxf(mmax, p.part_ml[((base + s) * p.Hq + head) * BM + r].x);
-    float4 acc = make_float4(0.f, 0.f, 0.f, 0.f);
-    float l = 0.f;
-    for (int s = 0; s < ns; ++s) {
-      float2 ml = p.part_ml[((base + s) * p.Hq + head) * BM + r];
-      float w = (ml.x == -INFINITY) ? 0.f : fast_exp2(ml.x - mmax);
-      l += ml.y * w;
-      float4 v = *reinterpret_cast<const float4*>(p.part_o + (((base + s) * p.Hq + head) * BM + r) * kD + c4);
-      acc.x += v.x * w; acc.y += v.y * w; acc.z += v.z * w; acc.w += v.w * w;
-    }
-    float inv = l > 0.f ? 1.f / l : 0.f;
-    __nv_bfloat16* og = p.out + (long long)(start + r0 + r) * p.o_stride + head * kD + c4;
-    uint2 packed = make_uint2(pack_bf16(acc.x * inv, acc.y * inv), pack_bf16(acc.z * inv, acc.w * inv));
-    *reinterpret_cast<uint2*>(og) = packed;
-    if (p.lse != nullptr && c4 == 0)
-      p.lse[(long long)head * p.total_T + start + r0 + r] = mmax * 0.6931471805599453f + logf(l);
+  const int r = rblk * kRowsPerCta + (threadIdx.x >> 5), c4 = (threadIdx.x & 31) * 4;
+  if (r0 + r > r1) return;
+  float mmax = -INFINITY;
+  for (int s = 0; s < ns; ++s)
+    mmax = fmaxf(mmax, p.part_ml[((base + s) * p.Hq + head) * BM + r].x);
+  float4 acc = make_float4(0.f, 0.f, 0.f, 0.f);
+  float l = 0.f;
+#pragma unroll 4
+  for (int s = 0; s < ns; ++s) {
+    float2 ml = p.part_ml[((base + s) * p.Hq + head) * BM + r];
+    float w = (ml.x == -INFINITY) ? 0.f : fast_exp2(ml.x - mmax);
+    l += ml.y * w;
+    float4 v = *reinterpret_cast<const float4*>(p.part_o + (((base + s) * p.Hq + head) * BM + r) * kD + c4);
+    acc.x += v.x * w; acc.y += v.y * w; acc.z += v.z * w; acc.w += v.w * w;
   }
+  float inv = l > 0.f ? 1.f / l : 0.f;
+  __nv_bfloat16* og = p.out + (long long)(start + r0 + r) * p.o_stride + head * kD + c4;
+  uint2 packed = make_uint2(pack_bf16(acc.x * inv, acc.y * inv), pack_bf16(acc.z * inv, acc.w * inv));
+  *reinterpret_cast<uint2*>(og) = packed;
+  if (p.lse != nullptr && c4 == 0)
+    p.lse[(long long)head * p.total_T + start + r0 + r] = mmax * 0.6931471805599453f + logf(l);
 }
 
 }  // namespace
@@ -383,13 +398,13 @@ int launch_attn_mma_t(const AttnParams& p, cudaStream_t s) {
     TMX_CUDA_TRY(cudaFuncSetAttribute(attn_mma_kernel<BM>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
     attr_set = true;
   }
-  int extra = p.last_tiles > 0 ? p.B * p.last_tiles * p.nsplit_max : 0;
+  int extra = (p.last_tiles > 0 && p.nsplit_max > 0) ? p.B * p.last_tiles * p.nsplit_max : 0;
   dim3 grid((unsigned)(p.n_slots + extra), (unsigned)p.Hq);
   attn_mma_kernel<BM><<<grid, BM * 2, smem, s>>>(p);
   count_launch();
   TMX_CUDA_TRY(cudaGetLastError());
   if (extra > 0) {
-    dim3 cg((unsigned)(p.B * p.last_tiles), (unsigned)p.Hq);
+    dim3 cg((unsigned)(p.B * p.last_tiles * (BM / 8)), (unsigned)p.Hq);
     combine_kernel<BM><<<cg, 256, 0, s>>>(p);
     count_launch();
     TMX_CUDA_TRY(cudaGetLastError());
