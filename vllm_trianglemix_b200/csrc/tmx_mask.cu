@@ -13,26 +13,56 @@ namespace {
 
 constexpr int kRowsPerCta = 8;  // 8 warps, one row each
 
+// Bits [lo, hi] (inclusive) of the 32-bit word whose LSB is column 0 of the span; 32-bit
+// arithmetic only (the 64-bit bit_span() of tmx_common.cuh made this kernel issue-bound:
+// ~160 instructions per 16-byte store, 2.76 TB/s at 128K).
+__device__ __forceinline__ uint32_t span32(int lo, int hi) {
+  lo = max(lo, 0);
+  hi = min(hi, 31);
+  const uint32_t upto = 0xffffffffu >> (31 - hi);         // hi in [0,31] when used
+  return hi < lo ? 0u : (upto & (0xffffffffu << lo));
+}
+
+// Every piece of every row is a union of at most two column intervals [a0,a1] U [b0,b1]
+// (row-uniform, computed once per warp).  A 128-column chunk that lies inside one interval
+// is all ones, one that meets neither is all zeros; only the <= 4 chunks per row holding an
+// interval end evaluate words.
 __global__ void __launch_bounds__(32 * kRowsPerCta)
 mask_bits_kernel(uint4* __restrict__ out, long long row_stride_vec, int n, int lrow, int si,
                  int sl, int piece) {
   long long row = (long long)blockIdx.x * kRowsPerCta + threadIdx.y;
   if (row >= n) return;
-  int i = (int)row;
+  const int i = (int)row;
   uint4* dst = out + row * row_stride_vec;
-  int words = (n + 31) >> 5;
-  for (long long vcol = threadIdx.x; vcol < row_stride_vec; vcol += 32) {
-    long long c0 = vcol * 128;
-    uint32_t w[4];
-#pragma unroll
-    for (int u = 0; u < 4; ++u) {
-      long long cw = c0 + 32 * u;
-      uint32_t bits = 0u;
-      if (cw <= i) bits = piece_word(piece, i, cw, n, lrow, si, sl);  // causal: nothing beyond i
-      w[u] = bits;
+  const int sink_hi = min(si, i);
+  const int win_lo = (int)max(0ll, (long long)i - sl);
+  const bool tail = i >= lrow;
+  int a0 = 0, a1 = -1, b0 = 0, b1 = -1;                    // empty
+  switch (piece) {
+    case TMX_PIECE_DENSE: a1 = i; break;
+    case TMX_PIECE_STREAMING: a1 = sink_hi; b0 = win_lo; b1 = i; break;
+    case TMX_PIECE_TRIANGLE:
+      if (tail) { a1 = i; } else { a1 = sink_hi; b0 = win_lo; b1 = i; }
+      break;
+    case TMX_PIECE_LAST: if (tail) { a0 = sink_hi + 1; a1 = win_lo - 1; } break;
+    default: if (!tail) { a0 = sink_hi + 1; a1 = win_lo - 1; } break;   // MIDDLE
+  }
+  const int nvec = (int)row_stride_vec;
+#pragma unroll 4
+  for (int vcol = threadIdx.x; vcol < nvec; vcol += 32) {
+    const int c0 = vcol * 128, c1 = c0 + 127;
+    uint4 w;
+    if ((c0 >= a0 && c1 <= a1) || (c0 >= b0 && c1 <= b1)) {
+      w = make_uint4(0xffffffffu, 0xffffffffu, 0xffffffffu, 0xffffffffu);
+    } else if ((c1 < a0 || c0 > a1) && (c1 < b0 || c0 > b1)) {
+      w = make_uint4(0u, 0u, 0u, 0u);
+    } else {
+      w.x = span32(a0 - c0, a1 - c0) | span32(b0 - c0, b1 - c0);
+      w.y = span32(a0 - c0 - 32, a1 - c0 - 32) | span32(b0 - c0 - 32, b1 - c0 - 32);
+      w.z = span32(a0 - c0 - 64, a1 - c0 - 64) | span32(b0 - c0 - 64, b1 - c0 - 64);
+      w.w = span32(a0 - c0 - 96, a1 - c0 - 96) | span32(b0 - c0 - 96, b1 - c0 - 96);
     }
-    (void)words;
-    __stcs(dst + vcol, make_uint4(w[0], w[1], w[2], w[3]));
+    __stcs(dst + vcol, w);
   }
 }
 
