@@ -61,12 +61,14 @@ struct Plan {
   int bm, bn;
   int stream;      // triangle layer: streaming tcgen05 kernel + mma kernel on the tail tiles only
   int stream_bm;   // tokens per streaming CTA
+  int tail_tc;     // dense tail rows on the tcgen05 split-KV path (else the mma.sync kernel)
+  int tail_bm;     // query-tile size of the tail path
   int n_slots, last_tiles, nsplit_max;
   size_t off_slots, off_part_o, off_part_ml, total;
 };
 
 Plan make_plan(int B, int total_T, int max_seqlen, int Hq, int Hkv, int si, int sl, int last, int mode,
-               int kernel, bool allow_stream) {
+               int kernel, bool allow_stream, bool allow_tail_tc) {
   Plan pl{};
   // AUTO: the tcgen05 kernel serves every tensor-bound case it can pair heads for (dense-causal
   // and unmasked layers).  Triangle layers are HBM-bound: their sink + window part goes to the
@@ -84,7 +86,16 @@ Plan make_plan(int B, int total_T, int max_seqlen, int Hq, int Hkv, int si, int 
   pl.stream_bm = pl.stream ? stream_block_m(Hq, Hkv) : 0;
   pl.n_slots = total_T / (pl.stream ? pl.stream_bm : pl.bm) + B;
   pl.last_tiles = 0; pl.nsplit_max = 0;
-  if (pl.kernel == TMX_KERNEL_MMA && mode == TMX_MODE_TRIANGLE) {
+  pl.tail_bm = pl.bm;
+  pl.tail_tc = pl.stream && allow_tail_tc && tail_tc_supported(Hq, Hkv, 1.0f) &&
+               last_tiles_max(last, tail_tc_block_m(Hq, Hkv)) > 0;
+  if (pl.tail_tc) {
+    // one CTA = all query heads of a KV head x one KV chunk; aim at one wave of CTAs
+    pl.tail_bm = tail_tc_block_m(Hq, Hkv);
+    pl.last_tiles = last_tiles_max(last, pl.tail_bm);
+    int ns = device_sm_count() / (B * Hkv > 0 ? B * Hkv : 1);
+    pl.nsplit_max = tail_nsplit(ceil_div(max_seqlen, 128), ns < 1 ? 1 : ns);
+  } else if (pl.kernel == TMX_KERNEL_MMA && mode == TMX_MODE_TRIANGLE) {
     int ns = nsplit_max(max_seqlen, pl.bn);
     int lt = last_tiles_max(last, pl.bm);
     if (lt > 0 && ceil_div(max_seqlen, pl.bn) >= kSplitMinTiles) { pl.last_tiles = lt; pl.nsplit_max = ns; }
@@ -93,8 +104,8 @@ Plan make_plan(int B, int total_T, int max_seqlen, int Hq, int Hkv, int si, int 
   size_t off = 0;
   pl.off_slots = off; off = align_up(off + sizeof(SlotInfo) * (size_t)pl.n_slots, 256);
   size_t parts = (size_t)B * pl.last_tiles * pl.nsplit_max * Hq;
-  pl.off_part_o = off; off = align_up(off + parts * pl.bm * 128 * sizeof(float), 256);
-  pl.off_part_ml = off; off = align_up(off + parts * pl.bm * sizeof(float2), 256);
+  pl.off_part_o = off; off = align_up(off + parts * pl.tail_bm * 128 * sizeof(float), 256);
+  pl.off_part_ml = off; off = align_up(off + parts * pl.tail_bm * sizeof(float2), 256);
   pl.total = off;
   return pl;
 }
@@ -132,9 +143,12 @@ extern "C" size_t tmx_attn_workspace_bytes(int B, int total_T, int max_seqlen, i
   (void)D;
   if (B <= 0 || total_T <= 0) return 256;
   // a bitmask (unknown here) disables the streaming plan: size for whichever plan is larger
-  const size_t a = make_plan(B, total_T, max_seqlen, Hq, Hkv, si, sl, last, mode, kernel, true).total;
-  const size_t b = make_plan(B, total_T, max_seqlen, Hq, Hkv, si, sl, last, mode, kernel, false).total;
-  return a > b ? a : b;
+  size_t best = 0;
+  for (int v = 0; v < 3; ++v) {
+    const size_t t = make_plan(B, total_T, max_seqlen, Hq, Hkv, si, sl, last, mode, kernel, v > 0, v > 1).total;
+    best = t > best ? t : best;
+  }
+  return best;
 }
 
 extern "C" int tmx_prefill_attn(void* out, const void* q, const void* k, const void* v,
@@ -161,7 +175,8 @@ extern "C" int tmx_prefill_attn(void* out, const void* q, const void* k, const v
   int st = check_arch();
   if (st != TMX_OK) return st;
 
-  Plan pl = make_plan(B, total_T, max_seqlen, Hq, Hkv, si, sl, last, mode, kernel, bitmask == nullptr);
+  Plan pl = make_plan(B, total_T, max_seqlen, Hq, Hkv, si, sl, last, mode, kernel, bitmask == nullptr,
+                      scale * 1.4426950408889634f > 0.f);
   if (!workspace || workspace_bytes < pl.total || mis(workspace)) return TMX_ERR_WORKSPACE;
   cudaStream_t s = (cudaStream_t)stream;
   uint8_t* ws = static_cast<uint8_t*>(workspace);
@@ -181,12 +196,13 @@ extern "C" int tmx_prefill_attn(void* out, const void* q, const void* k, const v
 
   if (pl.stream) {
     // triangle layer = streaming kernel (rows before the first tail tile) + tail tiles
-    p.tail_bm = pl.bm;
+    p.tail_bm = pl.tail_bm;
     st = build_slots(reinterpret_cast<SlotInfo*>(ws + pl.off_slots), pl.n_slots, cu_seqlens, B,
                      max_seqlen, pl.stream_bm, pl.bn, si, sl, last, mode, s);
     if (st != TMX_OK) return st;
     st = launch_attn_stream(p, s);
     if (st != TMX_OK || last <= 1 || pl.last_tiles == 0) return st;
+    if (pl.tail_tc) return launch_attn_tail_tc(p, s);
     p.tail_only = 1;
     p.n_slots = B * pl.last_tiles;
     return launch_attn_mma(p, pl.bm, s);

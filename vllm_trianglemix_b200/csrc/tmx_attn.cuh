@@ -34,6 +34,10 @@ int stream_block_m(int Hq, int Hkv);
 int launch_attn_stream(const AttnParams& p, cudaStream_t s);
 int launch_attn_sm100(const AttnParams& p, int variant, cudaStream_t s);      // 64-key tiles (v2)
 int launch_attn_sm100_v3(const AttnParams& p, int variant, cudaStream_t s);   // 128-key tiles (v3, default)
+// dense tail rows of triangle layers on the tensor cores (split-KV + merge, tmx_attn_sm100_v3.cu)
+bool tail_tc_supported(int Hq, int Hkv, float scale_log2);
+int tail_tc_block_m(int Hq, int Hkv);
+int launch_attn_tail_tc(const AttnParams& p, cudaStream_t s);
 // TMX_SM100_VARIANT env (developer switch), default 0: bit 7 selects the 64-key kernel, the low
 // bits are that kernel's own timing/emulation switches.
 int sm100_variant();

@@ -113,7 +113,16 @@ __device__ __forceinline__ uint64_t exp2_poly2(uint64_t t2) {
 // kEmu: how many of every 16 exponentials run on the FMA pipe (even: 0, 4, 6, 8).
 // kDbg (developer timing experiments, results are garbage): 1 = MMA/TMA side alone,
 // 2 = softmax side alone (S tile 0 computed once and re-read), 3 = group A alone (serial chain).
-template <int kEmu, int kDbg>
+//
+// kTail: split-KV worker for the dense tail rows of a TRIANGLE layer (the `last - 1` rows at the
+// end of every sequence attend all earlier keys: 2/3 of a 128K triangle layer's FLOPs sit in
+// its last 63 query rows).  The CTA then takes ALL G = 2P query heads of one KV head for a
+// tile of TT = 128 / P tokens -- packed row m of group g = token m / P, head h0 + g P + m % P,
+// loaded by a 3-D TMA box [64 d][P heads][TT tokens] that lands in the same K-major layout --
+// and one contiguous chunk of the KV tiles, and writes an fp32 partial (O, m, l) that
+// combine_tail_kernel merges.  K/V are therefore read once per KV head (not once per query
+// head) and the work spreads over ~148 CTAs instead of one.
+template <int kEmu, int kDbg, bool kTail>
 __global__ void __launch_bounds__(kThreads, 1)
 attn_sm100_v3_kernel(const AttnParams p, const __grid_constant__ TmaMaps maps) {
   extern __shared__ uint8_t smem_raw[];
@@ -127,16 +136,43 @@ attn_sm100_v3_kernel(const AttnParams p, const __grid_constant__ TmaMaps maps) {
   const int lane = threadIdx.x & 31;
 
   // ---- work item (uniform per CTA) -------------------------------------------
-  const SlotInfo slot = p.slots[p.n_slots - 1 - blockIdx.x];      // descending: longest first
-  if (slot.seq < 0) return;
-  const int n = slot.n, r0 = slot.q_tile * kBM;
-  const int r1 = min(n, r0 + kBM) - 1;
-  const int lo0 = slot.lo0, cnt0 = slot.hi0 - slot.lo0, lo1 = slot.lo1;
-  const int total = cnt0 + (slot.hi1 - slot.lo1);
-  const int seq_start = p.cu[slot.seq];
-  const int h0 = 2 * blockIdx.y;
-  const int kvh = h0 / (p.Hq / p.Hkv);
-  const int lrow = first_dense_row(n, p.last);
+  int n, r0, r1, lo0, cnt0, lo1, total, seq_start, h0, kvh, lrow;
+  int pshift = 0;          // log2(P): query heads packed per group (kTail only)
+  long long part = -1;     // split-KV partial index (kTail only)
+  if constexpr (kTail) {
+    const int G = p.Hq / p.Hkv;
+    pshift = (G >= 8) ? 2 : (G >= 4 ? 1 : 0);
+    const int TT = kBM >> pshift;
+    int e = blockIdx.x;
+    const int chunk = e % p.nsplit_max; e /= p.nsplit_max;
+    const int ql = e % p.last_tiles, seq = e / p.last_tiles;
+    seq_start = p.cu[seq];
+    n = p.cu[seq + 1] - seq_start;
+    lrow = first_dense_row(n, p.last);
+    if (n <= 0 || lrow >= n) return;
+    r0 = (lrow / TT + ql) * TT;
+    if (r0 >= n) return;
+    r1 = min(n, r0 + TT) - 1;
+    const int tiles = r1 / kBN + 1;
+    const int ns = tail_nsplit(tiles, p.nsplit_max);
+    if (chunk >= ns) return;
+    lo0 = (int)((long long)chunk * tiles / ns);
+    cnt0 = (int)((long long)(chunk + 1) * tiles / ns) - lo0;
+    lo1 = 0; total = cnt0;
+    kvh = blockIdx.y; h0 = kvh * G;
+    part = (long long)(seq * p.last_tiles + ql) * p.nsplit_max + chunk;
+  } else {
+    const SlotInfo slot = p.slots[p.n_slots - 1 - blockIdx.x];      // descending: longest first
+    if (slot.seq < 0) return;
+    n = slot.n; r0 = slot.q_tile * kBM;
+    r1 = min(n, r0 + kBM) - 1;
+    lo0 = slot.lo0; cnt0 = slot.hi0 - slot.lo0; lo1 = slot.lo1;
+    total = cnt0 + (slot.hi1 - slot.lo1);
+    seq_start = p.cu[slot.seq];
+    h0 = 2 * blockIdx.y;
+    kvh = h0 / (p.Hq / p.Hkv);
+    lrow = first_dense_row(n, p.last);
+  }
   auto tile_of = [&](int it) { return it < cnt0 ? lo0 + it : lo1 + (it - cnt0); };
 
   // ---- setup -------------------------------------------------------------------
@@ -164,8 +200,12 @@ attn_sm100_v3_kernel(const AttnParams p, const __grid_constant__ TmaMaps maps) {
       ptx::mbar_expect_tx(bar(bQFull), kQBytes);
       for (int g = 0; g < 2; ++g)
         for (int pnl = 0; pnl < 2; ++pnl)
-          ptx::tma_load_2d(sQ + (g * 2 + pnl) * (kBM * 128), &maps.q, bar(bQFull),
-                           (h0 + g) * kD + pnl * 64, seq_start + r0);
+          if constexpr (kTail)
+            ptx::tma_load_3d(sQ + (g * 2 + pnl) * (kBM * 128), &maps.q, bar(bQFull), pnl * 64,
+                             h0 + (g << pshift), seq_start + r0);
+          else
+            ptx::tma_load_2d(sQ + (g * 2 + pnl) * (kBM * 128), &maps.q, bar(bQFull),
+                             (h0 + g) * kD + pnl * 64, seq_start + r0);
       const int items = (kDbg == 2) ? 1 : 2 * total;     // item t: even = K(t/2), odd = V(t/2)
       int st = 0;
       for (int t = 0; t < items; ++t) {
@@ -263,8 +303,9 @@ attn_sm100_v3_kernel(const AttnParams p, const __grid_constant__ TmaMaps maps) {
     // =========================== softmax groups ===========================
     const int g = warp >> 2;                       // 0: head h0, 1: head h0 + 1
     const int row_in_tile = (warp & 3) * 32 + lane;
-    const int i = r0 + row_in_tile;                // query row inside the sequence
-    const int head = h0 + g;
+    // query row inside the sequence, and its head (kTail: P heads interleaved per token)
+    const int i = kTail ? r0 + (row_in_tile >> pshift) : r0 + row_in_tile;
+    const int head = kTail ? h0 + (g << pshift) + (row_in_tile & ((1 << pshift) - 1)) : h0 + g;
     const uint32_t lane_base = (uint32_t)((warp & 3) * 32) << 16;
     const uint32_t tS = tmem_base + lane_base + kColS + (uint32_t)(g * 128);
     const uint32_t tO = tmem_base + lane_base + kColO + (uint32_t)(g * 128);
@@ -278,8 +319,11 @@ attn_sm100_v3_kernel(const AttnParams p, const __grid_constant__ TmaMaps maps) {
       ptx::mbar_wait(bar(bSFull + g), kDbg == 2 ? 0 : (j & 1));
       ptx::tc_fence_after();
       const int c0 = tile_of(j) * kBN;
+      // (kTail: a dense tail row attends the whole tile as soon as the tile ends at or before it,
+      //  even when the tile also holds the few non-dense rows in front of the tail)
       const bool full = bm_row == nullptr &&
-                        tile_is_full(r0, r1, c0, c0 + kBN - 1, n, lrow, p.si, p.sl, p.mode);
+                        (tile_is_full(r0, r1, c0, c0 + kBN - 1, n, lrow, p.si, p.sl, p.mode) ||
+                         (kTail && i >= lrow && c0 + kBN - 1 <= i && i < n));
       uint32_t pk[64];             // the row's 128 probabilities as bf16 pairs
       float mx;                    // row max of the raw scores of this tile
       uint64_t sum2;               // two partial row sums
@@ -382,6 +426,25 @@ attn_sm100_v3_kernel(const AttnParams p, const __grid_constant__ TmaMaps maps) {
     // ---- epilogue: O / l -> bf16 -> global ------------------------------------
     if (!(kDbg == 3 && g == 1)) ptx::mbar_wait(bar(bOFull + g), 0);
     ptx::tc_fence_after();
+    if constexpr (kTail) {
+      // fp32 partial of this KV chunk: O (unnormalised), reference max (log2 domain), l
+      const int tt = kBM >> pshift;
+      const long long prow = (part * p.Hq + head) * tt + (i - r0);
+      float* po = p.part_o + prow * kD;
+#pragma unroll
+      for (int c = 0; c < 4; ++c) {
+        uint32_t r[32];
+        ptx::tmem_ld32(tO + c * 32, r);
+        ptx::tc_wait_ld();
+        if (i <= r1) {
+#pragma unroll
+          for (int v4 = 0; v4 < 8; ++v4)
+            *reinterpret_cast<uint4*>(po + c * 32 + v4 * 4) =
+                make_uint4(r[v4 * 4 + 0], r[v4 * 4 + 1], r[v4 * 4 + 2], r[v4 * 4 + 3]);
+        }
+      }
+      if (i <= r1) p.part_ml[prow] = make_float2(m_ref, l_run);
+    } else {
     const float inv = l_run > 0.f ? fast_rcp(l_run) : 0.f;
     __nv_bfloat16* orow = p.out + (long long)(seq_start + i) * p.o_stride + head * kD;
 #pragma unroll
@@ -403,6 +466,7 @@ attn_sm100_v3_kernel(const AttnParams p, const __grid_constant__ TmaMaps maps) {
     }
     if (p.lse != nullptr && i <= r1)
       p.lse[(long long)head * p.total_T + seq_start + i] = m_ref * 0.6931471805599453f + logf(l_run);
+    }
     ptx::tc_fence_before();
   }
 
@@ -414,7 +478,80 @@ attn_sm100_v3_kernel(const AttnParams p, const __grid_constant__ TmaMaps maps) {
   }
 }
 
+// Merge the split-KV partials of the tail tiles: one warp per (row, head), 4 columns per lane.
+__global__ void __launch_bounds__(256) combine_tail_kernel(const AttnParams p, const int tt) {
+  constexpr int kRowsPerCta = 8;
+  const int rblks = tt / kRowsPerCta;
+  int e = blockIdx.x / rblks;
+  const int rblk = blockIdx.x % rblks;
+  const int ql = e % p.last_tiles, seq = e / p.last_tiles;
+  const int head = blockIdx.y;
+  const int start = p.cu[seq], n = p.cu[seq + 1] - start;
+  const int lrow = first_dense_row(n, p.last);
+  if (n <= 0 || lrow >= n) return;
+  const int r0 = (lrow / tt + ql) * tt;
+  if (r0 >= n) return;
+  const int r1 = min(n, r0 + tt) - 1;
+  const int ns = tail_nsplit(r1 / kBN + 1, p.nsplit_max);
+  const long long base = (long long)(seq * p.last_tiles + ql) * p.nsplit_max;
+  const int r = rblk * kRowsPerCta + (threadIdx.x >> 5), c4 = (threadIdx.x & 31) * 4;
+  if (r0 + r > r1) return;
+  float mmax = -INFINITY;
+  for (int s = 0; s < ns; ++s)
+    mmax = fmaxf(mmax, p.part_ml[((base + s) * p.Hq + head) * tt + r].x);
+  float4 acc = make_float4(0.f, 0.f, 0.f, 0.f);
+  float l = 0.f;
+#pragma unroll 4
+  for (int s = 0; s < ns; ++s) {
+    const long long prow = ((base + s) * p.Hq + head) * tt + r;
+    const float2 ml = p.part_ml[prow];
+    const float w = (ml.x == -INFINITY) ? 0.f : fast_exp2(ml.x - mmax);
+    l += ml.y * w;
+    const float4 v = *reinterpret_cast<const float4*>(p.part_o + prow * kD + c4);
+    acc.x += v.x * w; acc.y += v.y * w; acc.z += v.z * w; acc.w += v.w * w;
+  }
+  const float inv = l > 0.f ? 1.f / l : 0.f;
+  __nv_bfloat16* og = p.out + (long long)(start + r0 + r) * p.o_stride + head * kD + c4;
+  *reinterpret_cast<uint2*>(og) = make_uint2(pack2(acc.x * inv, acc.y * inv), pack2(acc.z * inv, acc.w * inv));
+  if (p.lse != nullptr && c4 == 0)
+    p.lse[(long long)head * p.total_T + start + r0 + r] = mmax * 0.6931471805599453f + logf(l);
+}
+
 }  // namespace
+
+// Query-tile size (tokens) of the tcgen05 tail path: 2 groups x 128 packed rows = all G heads.
+int tail_tc_block_m(int Hq, int Hkv) { return 256 / (Hq / Hkv); }
+bool tail_tc_supported(int Hq, int Hkv, float scale_log2) {
+  if (Hkv <= 0 || Hq % Hkv != 0) return false;
+  const int G = Hq / Hkv;
+  return (G == 2 || G == 4 || G == 8) && scale_log2 > 0.f;
+}
+
+// Dense tail rows of a triangle layer: split-KV workers on the tensor cores + merge.
+// p.tail_bm = tail_tc_block_m(), p.last_tiles / p.nsplit_max from the plan.
+int launch_attn_tail_tc(const AttnParams& p, cudaStream_t s) {
+  const int G = p.Hq / p.Hkv, P = G / 2, TT = kBM / P;
+  auto kern = attn_sm100_v3_kernel<4, 0, true>;
+  static bool attr_set = false;
+  if (!attr_set) {
+    TMX_CUDA_TRY(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, kSmem));
+    attr_set = true;
+  }
+  TmaMaps maps;
+  int st = tma_map_q3d(&maps.q, p.q, p.total_T, p.Hq, p.q_stride, P, TT);
+  if (st == TMX_OK) st = tma_map_2d(&maps.k, p.k, p.total_T, (long long)p.Hkv * kD, p.kv_stride, kBN);
+  if (st == TMX_OK) st = tma_map_2d(&maps.v, p.v, p.total_T, (long long)p.Hkv * kD, p.kv_stride, kBN);
+  if (st != TMX_OK) return st;
+  dim3 grid((unsigned)(p.B * p.last_tiles * p.nsplit_max), (unsigned)p.Hkv);
+  kern<<<grid, kThreads, kSmem, s>>>(p, maps);
+  count_launch();
+  TMX_CUDA_TRY(cudaGetLastError());
+  dim3 cg((unsigned)(p.B * p.last_tiles * (TT / 8)), (unsigned)p.Hq);
+  combine_tail_kernel<<<cg, 256, 0, s>>>(p, TT);
+  count_launch();
+  TMX_CUDA_TRY(cudaGetLastError());
+  return TMX_OK;
+}
 
 int launch_attn_sm100_v3(const AttnParams& p, int variant, cudaStream_t s) {
   if ((p.Hq / p.Hkv) % 2 != 0) return TMX_ERR_UNSUPPORTED;   // needs two query heads per KV head
@@ -424,10 +561,10 @@ int launch_attn_sm100_v3(const AttnParams& p, int variant, cudaStream_t s) {
   const int emu = variant & 3, dbg = (variant >> 2) & 3;
   using Kern = void (*)(const AttnParams, const TmaMaps);
   static const Kern table[4][4] = {
-      {attn_sm100_v3_kernel<4, 0>, attn_sm100_v3_kernel<0, 0>, attn_sm100_v3_kernel<6, 0>, attn_sm100_v3_kernel<8, 0>},
-      {attn_sm100_v3_kernel<0, 1>, attn_sm100_v3_kernel<0, 1>, attn_sm100_v3_kernel<0, 1>, attn_sm100_v3_kernel<0, 1>},
-      {attn_sm100_v3_kernel<0, 2>, attn_sm100_v3_kernel<4, 2>, attn_sm100_v3_kernel<6, 2>, attn_sm100_v3_kernel<8, 2>},
-      {attn_sm100_v3_kernel<0, 3>, attn_sm100_v3_kernel<4, 3>, attn_sm100_v3_kernel<6, 3>, attn_sm100_v3_kernel<8, 3>}};
+      {attn_sm100_v3_kernel<4, 0, false>, attn_sm100_v3_kernel<0, 0, false>, attn_sm100_v3_kernel<6, 0, false>, attn_sm100_v3_kernel<8, 0, false>},
+      {attn_sm100_v3_kernel<0, 1, false>, attn_sm100_v3_kernel<0, 1, false>, attn_sm100_v3_kernel<0, 1, false>, attn_sm100_v3_kernel<0, 1, false>},
+      {attn_sm100_v3_kernel<0, 2, false>, attn_sm100_v3_kernel<4, 2, false>, attn_sm100_v3_kernel<6, 2, false>, attn_sm100_v3_kernel<8, 2, false>},
+      {attn_sm100_v3_kernel<0, 3, false>, attn_sm100_v3_kernel<4, 3, false>, attn_sm100_v3_kernel<6, 3, false>, attn_sm100_v3_kernel<8, 3, false>}};
   Kern kern = table[dbg][emu];
   TMX_CUDA_TRY(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, kSmem));
   TmaMaps maps;

@@ -48,13 +48,6 @@ __device__ __forceinline__ uint32_t pack2s(float lo, float hi) {
   __nv_bfloat162 v = __floats2bfloat162_rn(lo, hi);
   return *reinterpret_cast<uint32_t*>(&v);
 }
-__device__ __forceinline__ void tma_load_3d(uint32_t smem_dst, const void* tmap, uint32_t bar, int c0,
-                                            int c1, int c2) {
-  asm volatile(
-      "cp.async.bulk.tensor.3d.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%3, %4, %5}], [%2];"
-      ::"r"(smem_dst), "l"((uint64_t)tmap), "r"(bar), "r"(c0), "r"(c1), "r"(c2) : "memory");
-}
-
 __global__ void __launch_bounds__(kThreadsStream, 2)
 attn_stream_kernel(const AttnParams p, const __grid_constant__ StreamMaps maps, const int G, const int nW) {
   extern __shared__ uint8_t smem_raw[];
@@ -95,7 +88,7 @@ attn_stream_kernel(const AttnParams p, const __grid_constant__ StreamMaps maps, 
     if (ptx::elect_one()) {
       ptx::mbar_expect_tx(bIn, (uint32_t)(kQBytes + 2 * 2 * winPanel + 2 * 2 * kSinkKeys * 128));
       for (int pnl = 0; pnl < 2; ++pnl) {
-        tma_load_3d(sQ + pnl * (128 * 128), &maps.q, bIn, pnl * 64, kvh * G, seq_start + r0);
+        ptx::tma_load_3d(sQ + pnl * (128 * 128), &maps.q, bIn, pnl * 64, kvh * G, seq_start + r0);
         ptx::tma_load_2d(sKs + pnl * (kSinkKeys * 128), &maps.ks, bIn, kvh * kD + pnl * 64, seq_start);
         ptx::tma_load_2d(sKw + pnl * winPanel, &maps.kw, bIn, kvh * kD + pnl * 64, seq_start + w0);
         ptx::tma_load_2d(sVs + pnl * (kSinkKeys * 128), &maps.vs, bIn, kvh * kD + pnl * 64, seq_start);
@@ -217,25 +210,6 @@ attn_stream_kernel(const AttnParams p, const __grid_constant__ StreamMaps maps, 
     ptx::tc_fence_after();
     ptx::tmem_dealloc(tmem_base, 256);
   }
-}
-
-// [T][H][128] bf16 viewed as (d, head, token); box = 64 d x G heads x TT tokens, 128-byte swizzle
-int tma_map_q3d(CUtensorMap* m, const void* base, long long tokens, int heads, long long pitch_elems, int G,
-                int TT) {
-  auto enc = tma_encode_fn();
-  if (!enc) return TMX_ERR_CUDA;
-  cuuint64_t dims[3] = {(cuuint64_t)kD, (cuuint64_t)heads, (cuuint64_t)tokens};
-  cuuint64_t strides[2] = {(cuuint64_t)kD * 2, (cuuint64_t)pitch_elems * 2};
-  cuuint32_t box[3] = {64u, (cuuint32_t)G, (cuuint32_t)TT};
-  cuuint32_t estr[3] = {1u, 1u, 1u};
-  CUresult r = enc(m, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 3, const_cast<void*>(base), dims, strides, box, estr,
-                   CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B,
-                   CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
-  if (r != CUDA_SUCCESS) {
-    set_cuda_error(cudaErrorInvalidValue, "cuTensorMapEncodeTiled(q3d)");
-    return TMX_ERR_CUDA;
-  }
-  return TMX_OK;
 }
 
 }  // namespace

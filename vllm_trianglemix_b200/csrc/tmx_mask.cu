@@ -19,8 +19,8 @@ constexpr int kRowsPerCta = 8;  // 8 warps, one row each
 __device__ __forceinline__ uint32_t span32(int lo, int hi) {
   lo = max(lo, 0);
   hi = min(hi, 31);
-  const uint32_t upto = 0xffffffffu >> (31 - hi);         // hi in [0,31] when used
-  return hi < lo ? 0u : (upto & (0xffffffffu << lo));
+  if (hi < lo) return 0u;                                 // from here 0 <= lo <= hi <= 31
+  return (0xffffffffu >> (31 - hi)) & (0xffffffffu << lo);
 }
 
 // Every piece of every row is a union of at most two column intervals [a0,a1] U [b0,b1]

@@ -40,6 +40,15 @@ __host__ __device__ __forceinline__ int nsplit_max(int max_seqlen, int bn) {
   return ceil_div(ceil_div(max_seqlen, bn), kSplitTiles);
 }
 
+// tcgen05 tail path: a tail tile touching `tiles` 128-key KV tiles is cut into this many
+// contiguous chunks (at least kTailMinTiles tiles each, at most the plan's nsplit_max).
+constexpr int kTailMinTiles = 4;
+__host__ __device__ __forceinline__ int tail_nsplit(int tiles, int nsplit_max) {
+  int ns = tiles / kTailMinTiles;
+  ns = ns < 1 ? 1 : ns;
+  return ns < nsplit_max ? ns : nsplit_max;
+}
+
 // Does query tile q (rows [r0, r1]) of a length-n sequence get split?  Returns nsplit or 0.
 __host__ __device__ __forceinline__ int split_count(int r0, int r1, int n, int bn, int lrow,
                                                     int last, int mode, int bm) {

@@ -44,4 +44,24 @@ inline int tma_map_2d(CUtensorMap* m, const void* base, long long rows, long lon
   return TMX_OK;
 }
 
+// [T][H][128] bf16 viewed as (d, head, token); box = 64 d x G heads x TT tokens, 128-byte swizzle
+inline int tma_map_q3d(CUtensorMap* m, const void* base, long long tokens, int heads, long long pitch_elems, int G,
+                int TT) {
+  auto enc = tma_encode_fn();
+  if (!enc) return TMX_ERR_CUDA;
+  cuuint64_t dims[3] = {(cuuint64_t)128, (cuuint64_t)heads, (cuuint64_t)tokens};
+  cuuint64_t strides[2] = {(cuuint64_t)128 * 2, (cuuint64_t)pitch_elems * 2};
+  cuuint32_t box[3] = {64u, (cuuint32_t)G, (cuuint32_t)TT};
+  cuuint32_t estr[3] = {1u, 1u, 1u};
+  CUresult r = enc(m, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 3, const_cast<void*>(base), dims, strides, box, estr,
+                   CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B,
+                   CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+  if (r != CUDA_SUCCESS) {
+    set_cuda_error(cudaErrorInvalidValue, "cuTensorMapEncodeTiled(q3d)");
+    return TMX_ERR_CUDA;
+  }
+  return TMX_OK;
+}
+
+
 }  // namespace tmx
