@@ -92,7 +92,7 @@ Plan make_plan(int B, int total_T, int max_seqlen, int Hq, int Hkv, int si, int 
   if (pl.tail_tc) {
     // one CTA = all query heads of a KV head x one KV chunk; aim at one wave of CTAs
     pl.tail_bm = tail_tc_block_m(Hq, Hkv);
-    pl.last_tiles = last_tiles_max(last, pl.tail_bm);
+    pl.last_tiles = ceil_div(last - 1, pl.tail_bm);      // tail tiles start at the first dense row
     int ns = device_sm_count() / (B * Hkv > 0 ? B * Hkv : 1);
     pl.nsplit_max = tail_nsplit(ceil_div(max_seqlen, 128), ns < 1 ? 1 : ns);
   } else if (pl.kernel == TMX_KERNEL_MMA && mode == TMX_MODE_TRIANGLE) {
@@ -196,7 +196,9 @@ extern "C" int tmx_prefill_attn(void* out, const void* q, const void* k, const v
 
   if (pl.stream) {
     // triangle layer = streaming kernel (rows before the first tail tile) + tail tiles
-    p.tail_bm = pl.tail_bm;
+    // rows the streaming kernel leaves to the tail path start at a multiple of p.tail_bm: the
+    // tcgen05 tail tiles begin exactly at the first dense row (1), the mma.sync ones are aligned
+    p.tail_bm = pl.tail_tc ? 1 : pl.tail_bm;
     st = build_slots(reinterpret_cast<SlotInfo*>(ws + pl.off_slots), pl.n_slots, cu_seqlens, B,
                      max_seqlen, pl.stream_bm, pl.bn, si, sl, last, mode, s);
     if (st != TMX_OK) return st;

@@ -150,7 +150,7 @@ attn_sm100_v3_kernel(const AttnParams p, const __grid_constant__ TmaMaps maps) {
     n = p.cu[seq + 1] - seq_start;
     lrow = first_dense_row(n, p.last);
     if (n <= 0 || lrow >= n) return;
-    r0 = (lrow / TT + ql) * TT;
+    r0 = lrow + ql * TT;           // tail tiles start AT the first dense row: every row is dense
     if (r0 >= n) return;
     r1 = min(n, r0 + TT) - 1;
     const int tiles = r1 / kBN + 1;
@@ -208,7 +208,27 @@ attn_sm100_v3_kernel(const AttnParams p, const __grid_constant__ TmaMaps maps) {
                              (h0 + g) * kD + pnl * 64, seq_start + r0);
       const int items = (kDbg == 2) ? 1 : 2 * total;     // item t: even = K(t/2), odd = V(t/2)
       int st = 0;
+      // kTail streams K/V from HBM (no reuse across CTAs).  A CTA's own TMA boxes are 128-byte
+      // pieces at a pitch of Hkv * 256 bytes; the Hkv CTAs of a chunk together cover whole rows.
+      // Each of them therefore pulls its 1/Hkv share of the rows of a tile kPfDist tiles ahead
+      // into L2 at FULL row width (contiguous Hkv * 256-byte bursts), so that DRAM sees long
+      // sequential reads and the later box loads of all Hkv CTAs hit L2.
+      constexpr int kPfDist = 4;
+      const int pf_rows = (kBN + p.Hkv - 1) / p.Hkv;
+      auto prefetch_tile = [&](int idx) {
+        if (idx >= total) return;
+        const int rbeg = kvh * pf_rows, rend = min(kBN, rbeg + pf_rows);
+        const long long tok0 = (long long)seq_start + (long long)tile_of(idx) * kBN;
+        for (int r = rbeg; r < rend; ++r) {
+          if (tok0 + r >= p.total_T) break;
+          ptx::prefetch_l2(p.k + (tok0 + r) * p.kv_stride, (uint32_t)(p.Hkv * kD * 2));
+          ptx::prefetch_l2(p.v + (tok0 + r) * p.kv_stride, (uint32_t)(p.Hkv * kD * 2));
+        }
+      };
+      if constexpr (kTail)
+        for (int d = 0; d < kPfDist; ++d) prefetch_tile(d);
       for (int t = 0; t < items; ++t) {
+        if constexpr (kTail) { if ((t & 1) == 0) prefetch_tile((t >> 1) + kPfDist); }
         if (t >= kStages) ptx::mbar_wait(bar(bEmpty + st), ((t / kStages) - 1) & 1);
         ptx::mbar_expect_tx(bar(bFull + st), kTileBytes);
         const int row = seq_start + tile_of(t >> 1) * kBN;
@@ -319,11 +339,8 @@ attn_sm100_v3_kernel(const AttnParams p, const __grid_constant__ TmaMaps maps) {
       ptx::mbar_wait(bar(bSFull + g), kDbg == 2 ? 0 : (j & 1));
       ptx::tc_fence_after();
       const int c0 = tile_of(j) * kBN;
-      // (kTail: a dense tail row attends the whole tile as soon as the tile ends at or before it,
-      //  even when the tile also holds the few non-dense rows in front of the tail)
       const bool full = bm_row == nullptr &&
-                        (tile_is_full(r0, r1, c0, c0 + kBN - 1, n, lrow, p.si, p.sl, p.mode) ||
-                         (kTail && i >= lrow && c0 + kBN - 1 <= i && i < n));
+                        tile_is_full(r0, r1, c0, c0 + kBN - 1, n, lrow, p.si, p.sl, p.mode);
       uint32_t pk[64];             // the row's 128 probabilities as bf16 pairs
       float mx;                    // row max of the raw scores of this tile
       uint64_t sum2;               // two partial row sums
@@ -344,15 +361,10 @@ attn_sm100_v3_kernel(const AttnParams p, const __grid_constant__ TmaMaps maps) {
           for (int e = 0; e < 32; ++e) x[e] = __uint_as_float(xr[e]);
           if (!full) {
             const int cb = c0 + c * 32;
-            if (bm_row == nullptr) {
+            const uint32_t bits = bm_row != nullptr ? bm_row[cb >> 5]
+                                                    : mask_word32(i, cb, n, lrow, p.si, p.sl, p.mode);
 #pragma unroll
-              for (int e = 0; e < 32; ++e)
-                x[e] = attends(i, cb + e, n, lrow, p.si, p.sl, p.mode) ? x[e] : -INFINITY;
-            } else {
-              const uint32_t bits = bm_row[cb >> 5];
-#pragma unroll
-              for (int e = 0; e < 32; ++e) x[e] = ((bits >> e) & 1u) ? x[e] : -INFINITY;
-            }
+            for (int e = 0; e < 32; ++e) x[e] = ((bits >> e) & 1u) ? x[e] : -INFINITY;
           }
 #pragma unroll
           for (int e = 0; e < 32; e += 4) {
@@ -489,7 +501,7 @@ __global__ void __launch_bounds__(256) combine_tail_kernel(const AttnParams p, c
   const int start = p.cu[seq], n = p.cu[seq + 1] - start;
   const int lrow = first_dense_row(n, p.last);
   if (n <= 0 || lrow >= n) return;
-  const int r0 = (lrow / tt + ql) * tt;
+  const int r0 = lrow + ql * tt;
   if (r0 >= n) return;
   const int r1 = min(n, r0 + tt) - 1;
   const int ns = tail_nsplit(r1 / kBN + 1, p.nsplit_max);

@@ -59,12 +59,14 @@ attn_stream_kernel(const AttnParams p, const __grid_constant__ StreamMaps maps, 
   const int warp = __shfl_sync(0xffffffffu, (int)(threadIdx.x >> 5), 0);
   const int lane = threadIdx.x & 31;
 
-  const SlotInfo slot = p.slots[blockIdx.x];
+  // launch order: the Hkv CTAs of one token tile are neighbours (they read / write adjacent
+  // pieces of the same token rows, so DRAM sees whole rows at about the same time)
+  const int kvh = (int)(blockIdx.x % (unsigned)p.Hkv);
+  const SlotInfo slot = p.slots[blockIdx.x / (unsigned)p.Hkv];
   if (slot.seq < 0) return;
   const int TT = 128 / G;
   const int n = slot.n, r0 = slot.q_tile * TT;
   const int seq_start = p.cu[slot.seq];
-  const int kvh = blockIdx.y;
   const int w0 = r0 - p.sl;                       // first window key (may be negative: masked)
   // rows >= stream_end belong to query tiles the dense-tail path owns
   const int lrow = first_dense_row(n, p.last);
@@ -242,7 +244,7 @@ int launch_attn_stream(const AttnParams& p, cudaStream_t s) {
   if (st == TMX_OK) st = tma_map_2d(&maps.ks, p.k, p.total_T, (long long)p.Hkv * kD, p.kv_stride, kSinkKeys);
   if (st == TMX_OK) st = tma_map_2d(&maps.vs, p.v, p.total_T, (long long)p.Hkv * kD, p.kv_stride, kSinkKeys);
   if (st != TMX_OK) return st;
-  dim3 grid((unsigned)p.n_slots, (unsigned)p.Hkv);
+  dim3 grid((unsigned)p.n_slots * (unsigned)p.Hkv);
   attn_stream_kernel<<<grid, kThreadsStream, kSmemStream, s>>>(p, maps, G, nW);
   count_launch();
   TMX_CUDA_TRY(cudaGetLastError());

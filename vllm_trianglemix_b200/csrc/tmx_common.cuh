@@ -53,6 +53,27 @@ __host__ __device__ __forceinline__ uint32_t bit_span(long long lo, long long hi
   return upto_hi & ~((1u << lo) - 1u);
 }
 
+// Same in 32-bit arithmetic (|lo|, |hi| < 2^31): the form the attention kernels use per tile.
+__host__ __device__ __forceinline__ uint32_t bit_span32(int lo, int hi) {
+  lo = lo < 0 ? 0 : lo;
+  hi = hi > 31 ? 31 : hi;
+  if (hi < lo) return 0u;                                 // from here 0 <= lo <= hi <= 31
+  return (0xffffffffu >> (31 - hi)) & (0xffffffffu << lo);
+}
+
+// Attention mask of query row i for the 32 key columns [c0, c0 + 32) as a word (bit e = column
+// c0 + e), same predicate as attends().  One word per 32 scores replaces 32 predicate
+// evaluations in the kernels' partial tiles.
+__host__ __device__ __forceinline__ uint32_t mask_word32(int i, int c0, int n, int lrow, int si, int sl,
+                                                         int mode) {
+  if (mode == TMX_MODE_NONE) return bit_span32(-c0, n - 1 - c0);
+  const uint32_t causal = bit_span32(-c0, i - c0);
+  if (mode == TMX_MODE_DENSE_CAUSAL || i >= lrow) return causal;
+  const int wlo = sl > i ? 0 : i - sl;
+  const int shi = si < i ? si : i;
+  return causal & (bit_span32(-c0, shi - c0) | bit_span32(wlo - c0, i - c0));
+}
+
 // 32 columns [c0, c0+32) of row i of a piece, as a word (LSB = column c0).
 // Closed form: each row's attended set is a union of at most two intervals.
 __host__ __device__ __forceinline__ uint32_t piece_word(int piece, int i, long long c0,

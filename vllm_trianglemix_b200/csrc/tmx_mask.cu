@@ -13,16 +13,8 @@ namespace {
 
 constexpr int kRowsPerCta = 8;  // 8 warps, one row each
 
-// Bits [lo, hi] (inclusive) of the 32-bit word whose LSB is column 0 of the span; 32-bit
-// arithmetic only (the 64-bit bit_span() of tmx_common.cuh made this kernel issue-bound:
-// ~160 instructions per 16-byte store, 2.76 TB/s at 128K).
-__device__ __forceinline__ uint32_t span32(int lo, int hi) {
-  lo = max(lo, 0);
-  hi = min(hi, 31);
-  if (hi < lo) return 0u;                                 // from here 0 <= lo <= hi <= 31
-  return (0xffffffffu >> (31 - hi)) & (0xffffffffu << lo);
-}
-
+// (32-bit interval words: the 64-bit bit_span() of tmx_common.cuh made this kernel issue-bound,
+// ~160 instructions per 16-byte store, 2.76 TB/s at 128K.)
 // Every piece of every row is a union of at most two column intervals [a0,a1] U [b0,b1]
 // (row-uniform, computed once per warp).  A 128-column chunk that lies inside one interval
 // is all ones, one that meets neither is all zeros; only the <= 4 chunks per row holding an
@@ -57,10 +49,10 @@ mask_bits_kernel(uint4* __restrict__ out, long long row_stride_vec, int n, int l
     } else if ((c1 < a0 || c0 > a1) && (c1 < b0 || c0 > b1)) {
       w = make_uint4(0u, 0u, 0u, 0u);
     } else {
-      w.x = span32(a0 - c0, a1 - c0) | span32(b0 - c0, b1 - c0);
-      w.y = span32(a0 - c0 - 32, a1 - c0 - 32) | span32(b0 - c0 - 32, b1 - c0 - 32);
-      w.z = span32(a0 - c0 - 64, a1 - c0 - 64) | span32(b0 - c0 - 64, b1 - c0 - 64);
-      w.w = span32(a0 - c0 - 96, a1 - c0 - 96) | span32(b0 - c0 - 96, b1 - c0 - 96);
+      w.x = bit_span32(a0 - c0, a1 - c0) | bit_span32(b0 - c0, b1 - c0);
+      w.y = bit_span32(a0 - c0 - 32, a1 - c0 - 32) | bit_span32(b0 - c0 - 32, b1 - c0 - 32);
+      w.z = bit_span32(a0 - c0 - 64, a1 - c0 - 64) | bit_span32(b0 - c0 - 64, b1 - c0 - 64);
+      w.w = bit_span32(a0 - c0 - 96, a1 - c0 - 96) | bit_span32(b0 - c0 - 96, b1 - c0 - 96);
     }
     __stcs(dst + vcol, w);
   }

@@ -80,6 +80,11 @@ __device__ __forceinline__ void tma_load_3d(uint32_t smem_dst, const void* tmap,
       ::"r"(smem_dst), "l"((uint64_t)tmap), "r"(bar), "r"(c0), "r"(c1), "r"(c2) : "memory");
 }
 
+// bulk prefetch of [addr, addr + bytes) into L2 (bytes % 16 == 0, addr 16-byte aligned)
+__device__ __forceinline__ void prefetch_l2(const void* addr, uint32_t bytes) {
+  asm volatile("cp.async.bulk.prefetch.L2.global [%0], %1;" ::"l"(addr), "r"(bytes) : "memory");
+}
+
 // ---- tcgen05 ----------------------------------------------------------------------------
 __device__ __forceinline__ void tmem_alloc(uint32_t smem_result, uint32_t ncols) {
   asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_result), "r"(ncols) : "memory");
