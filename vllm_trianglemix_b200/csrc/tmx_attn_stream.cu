@@ -49,7 +49,8 @@ __device__ __forceinline__ uint32_t pack2s(float lo, float hi) {
   return *reinterpret_cast<uint32_t*>(&v);
 }
 __global__ void __launch_bounds__(kThreadsStream, 2)
-attn_stream_kernel(const AttnParams p, const __grid_constant__ StreamMaps maps, const int G, const int nW) {
+attn_stream_kernel(const AttnParams p, const __grid_constant__ StreamMaps maps, const int G, const int nW,
+                   const unsigned pf_stride) {
   extern __shared__ uint8_t smem_raw[];
   const uint32_t smem_base = (ptx::smem_u32(smem_raw) + 1023u) & ~1023u;
   const uint32_t sQ = smem_base, sKw = smem_base + kOffKw, sVw = smem_base + kOffVw;
@@ -95,6 +96,23 @@ attn_stream_kernel(const AttnParams p, const __grid_constant__ StreamMaps maps, 
         ptx::tma_load_2d(sKw + pnl * winPanel, &maps.kw, bIn, kvh * kD + pnl * 64, seq_start + w0);
         ptx::tma_load_2d(sVs + pnl * (kSinkKeys * 128), &maps.vs, bIn, kvh * kD + pnl * 64, seq_start);
         ptx::tma_load_2d(sVw + pnl * winPanel, &maps.vw, bIn, kvh * kD + pnl * 64, seq_start + w0);
+      }
+      // The CTA is one serial chain (load -> S -> softmax -> PV -> store) and only two fit an SM
+      // (TMEM), so HBM latency sits on the critical path.  Pull the inputs of the CTA that will
+      // run on this SM slot about one wave from now (same KV head: the stride is a multiple of
+      // Hkv) into L2 now; its TMA loads then see L2 latency instead of DRAM latency.
+      const unsigned nxt = blockIdx.x + pf_stride;
+      if (nxt < gridDim.x) {
+        const SlotInfo s2 = p.slots[nxt / (unsigned)p.Hkv];
+        if (s2.seq >= 0) {
+          const long long t0 = (long long)p.cu[s2.seq] + (long long)s2.q_tile * TT;
+          const long long t1 = min(t0 + TT, (long long)p.total_T);
+          for (long long tok = t0; tok < t1; ++tok) {
+            ptx::prefetch_l2(p.q + tok * p.q_stride + (long long)kvh * G * kD, (uint32_t)(G * kD * 2));
+            ptx::prefetch_l2(p.k + tok * p.kv_stride + (long long)kvh * kD, (uint32_t)(kD * 2));
+            ptx::prefetch_l2(p.v + tok * p.kv_stride + (long long)kvh * kD, (uint32_t)(kD * 2));
+          }
+        }
       }
     }
     __syncwarp();
@@ -245,7 +263,10 @@ int launch_attn_stream(const AttnParams& p, cudaStream_t s) {
   if (st == TMX_OK) st = tma_map_2d(&maps.vs, p.v, p.total_T, (long long)p.Hkv * kD, p.kv_stride, kSinkKeys);
   if (st != TMX_OK) return st;
   dim3 grid((unsigned)p.n_slots * (unsigned)p.Hkv);
-  attn_stream_kernel<<<grid, kThreadsStream, kSmemStream, s>>>(p, maps, G, nW);
+  // CTAs resident at a time (2 per SM), rounded to a multiple of Hkv: the L2 prefetch distance
+  unsigned pf = 2u * (unsigned)device_sm_count();
+  pf = (pf + (unsigned)p.Hkv - 1) / (unsigned)p.Hkv * (unsigned)p.Hkv;
+  attn_stream_kernel<<<grid, kThreadsStream, kSmemStream, s>>>(p, maps, G, nW, pf);
   count_launch();
   TMX_CUDA_TRY(cudaGetLastError());
   return TMX_OK;
