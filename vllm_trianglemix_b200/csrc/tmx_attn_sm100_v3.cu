@@ -46,7 +46,9 @@ constexpr int bEmpty = bFull + kStages;           // [kStages]
 constexpr int bSFull = bEmpty + kStages;          // [2 groups]
 constexpr int bPReady = bSFull + 2;               // [2 groups], 4 arrivals (one per warp)
 constexpr int bOFull = bPReady + 2;               // [2 groups]
-constexpr int kNumBars = bOFull + 2;
+constexpr int bP1Ready = bOFull + 2;              // [2 groups] kSplitP: second half of P stored
+constexpr int bPV0Done = bP1Ready + 2;            // [2 groups] kSplitP: first half of PV(j) complete
+constexpr int kNumBars = bPV0Done + 2;
 constexpr int kSmem = kOffBar + kNumBars * 8 + 16 + 1024;   // + alignment slack
 static_assert(kSmem <= 232448, "exceeds the 227 KB of shared memory a CTA may use");
 
@@ -122,7 +124,11 @@ __device__ __forceinline__ uint64_t exp2_poly2(uint64_t t2) {
 // and one contiguous chunk of the KV tiles, and writes an fp32 partial (O, m, l) that
 // combine_tail_kernel merges.  K/V are therefore read once per KV head (not once per query
 // head) and the work spreads over ~148 CTAs instead of one.
-template <int kEmu, int kDbg, bool kTail>
+//
+// kSplitP: P is stored in two halves (keys [0,64) and [64,128) of the tile); the MMA warp issues
+// the first four k-steps of PV as soon as the first half is there, so that only HALF a PV (plus
+// the next score MMA) sits between the end of a group's exponentials and its next S tile.
+template <int kEmu, int kDbg, bool kTail, bool kSplitP>
 __global__ void __launch_bounds__(kThreads, 1)
 attn_sm100_v3_kernel(const AttnParams p, const __grid_constant__ TmaMaps maps) {
   extern __shared__ uint8_t smem_raw[];
@@ -184,6 +190,8 @@ attn_sm100_v3_kernel(const AttnParams p, const __grid_constant__ TmaMaps maps) {
       ptx::mbar_init(bar(bSFull + g), 1);
       ptx::mbar_init(bar(bPReady + g), 4);       // one arrive per softmax warp of the group
       ptx::mbar_init(bar(bOFull + g), 1);
+      ptx::mbar_init(bar(bP1Ready + g), 4);
+      ptx::mbar_init(bar(bPV0Done + g), 1);
     }
     ptx::fence_barrier_init();
   }
@@ -263,12 +271,12 @@ attn_sm100_v3_kernel(const AttnParams p, const __grid_constant__ TmaMaps maps) {
       }
     };
     // O_g += P_g V: 8 k-steps of 16 keys; P (bf16) read from columns [0,64) of S_g
-    auto issue_pv = [&](int g, int st, bool acc) {
+    auto issue_pv = [&](int g, int st, bool acc, int ks0 = 0, int ks1 = kBN / 16) {
       const uint32_t d_tmem = tb + kColO + (uint32_t)(g * 128);
       const uint32_t a_tmem = tb + kColS + (uint32_t)(g * 128);
       const uint64_t vb = dV + (uint64_t)((st * kTileBytes) >> 4);
 #pragma unroll
-      for (int ks = 0; ks < kBN / 16; ++ks)
+      for (int ks = ks0; ks < ks1; ++ks)
         ptx::mma_ts(d_tmem, a_tmem + (uint32_t)(ks * 8), vb + (uint64_t)((ks * 2048) >> 4), kIdescO,
                     acc || ks > 0);
     };
@@ -302,12 +310,28 @@ attn_sm100_v3_kernel(const AttnParams p, const __grid_constant__ TmaMaps maps) {
         }
         if (kDbg != 1) ptx::mbar_wait(bar(bPReady + g), j & 1);
         ptx::tc_fence_after();
+        if constexpr (kSplitP) {
+          if (ptx::elect_one()) {
+            issue_pv(g, vst, j > 0, 0, 4);
+            ptx::mma_commit(bar(bPV0Done + g));
+          }
+          __syncwarp();
+          if (kDbg != 1) ptx::mbar_wait(bar(bP1Ready + g), j & 1);
+          ptx::tc_fence_after();
+          if (ptx::elect_one()) {
+            issue_pv(g, vst, true, 4, 8);
+            if (!more) ptx::mma_commit(bar(bOFull + g));
+            if (g == 1) ptx::mma_commit(bar(bEmpty + vst));
+          }
+          __syncwarp();
+        } else {
         if (ptx::elect_one()) {
           issue_pv(g, vst, j > 0);
           if (!more) ptx::mma_commit(bar(bOFull + g));
           if (g == 1) ptx::mma_commit(bar(bEmpty + vst));
         }
         __syncwarp();
+        }
         if (more) {
           if (g == 0) { ptx::mbar_wait(bar(bFull + kst), kph); ptx::tc_fence_after(); }
           if (ptx::elect_one()) {
@@ -341,6 +365,97 @@ attn_sm100_v3_kernel(const AttnParams p, const __grid_constant__ TmaMaps maps) {
       const int c0 = tile_of(j) * kBN;
       const bool full = bm_row == nullptr &&
                         tile_is_full(r0, r1, c0, c0 + kBN - 1, n, lrow, p.si, p.sl, p.mode);
+      if constexpr (kSplitP) {
+        // Two halves of 64 keys, each an optimistic pass of its own against the current reference
+        // max.  A refresh in the second half rescales O after PV's first half (already issued
+        // with the old reference) has completed: O, l and the first half's sum all scale by alpha.
+        float sum_a = 0.f;
+#pragma unroll
+        for (int h = 0; h < 2; ++h) {
+          uint32_t ph[32];           // 64 probabilities as bf16 pairs
+          float sum_h;
+#pragma unroll 1
+          for (int attempt = 0;; ++attempt) {
+            const float neg_m = (m_ref == -INFINITY) ? 0.f : -m_ref;
+            const uint64_t negm2 = pk_f2(neg_m, neg_m);
+            float mx0 = -INFINITY, mx1 = -INFINITY;
+            uint64_t sum2 = pk_f2(0.f, 0.f);
+            auto chunk = [&](int c, uint32_t (&xr)[32]) {
+              float x[32];
+#pragma unroll
+              for (int e = 0; e < 32; ++e) x[e] = __uint_as_float(xr[e]);
+              if (!full) {
+                const int cb = c0 + c * 32;
+                const uint32_t bits = bm_row != nullptr ? bm_row[cb >> 5]
+                                                        : mask_word32(i, cb, n, lrow, p.si, p.sl, p.mode);
+#pragma unroll
+                for (int e = 0; e < 32; ++e) x[e] = ((bits >> e) & 1u) ? x[e] : -INFINITY;
+              }
+#pragma unroll
+              for (int e = 0; e < 32; e += 4) {
+                mx0 = fmaxf(mx0, fmaxf(x[e], x[e + 1]));
+                mx1 = fmaxf(mx1, fmaxf(x[e + 2], x[e + 3]));
+              }
+#pragma unroll
+              for (int e = 0; e < 32; e += 2) {
+                uint64_t q2 = ffma2(pk_f2(x[e], x[e + 1]), sc2, negm2);
+                float a, b;
+                if ((e & 15) < kEmu) {
+                  q2 = exp2_poly2(q2);
+                  upk_f2(q2, a, b);
+                } else {
+                  upk_f2(q2, a, b);
+                  a = fast_exp2(a);
+                  b = fast_exp2(b);
+                  q2 = pk_f2(a, b);
+                }
+                sum2 = fadd2(sum2, q2);
+                ph[(c & 1) * 16 + e / 2] = pack2(a, b);
+              }
+            };
+            uint32_t xa[32], xb[32];
+            ptx::tmem_ld32(tS + h * 64, xa);
+            ptx::tc_wait_ld();
+            ptx::tmem_ld32(tS + h * 64 + 32, xb);      // in flight while the first chunk is processed
+            chunk(2 * h, xa);
+            ptx::tc_wait_ld();
+            chunk(2 * h + 1, xb);
+            const float m_new = fmaxf(m_ref, fmaxf(mx0, mx1) * sc);
+            const bool grow = (m_new > m_ref + 8.0f) || (m_ref == -INFINITY && m_new > -INFINITY);
+            {
+              float a, b;
+              upk_f2(sum2, a, b);
+              sum_h = a + b;
+            }
+            if (attempt == 1 || !__any_sync(0xffffffffu, grow)) break;
+            if (j > 0 || h == 1) {
+              // h == 0: S(j) complete => PV(j-1) complete; h == 1: wait for the first half of PV(j)
+              if (h == 1 && kDbg != 2) { ptx::mbar_wait(bar(bPV0Done + g), j & 1); ptx::tc_fence_after(); }
+              const float alpha = (m_new == -INFINITY) ? 1.0f : fast_exp2(m_ref - m_new);
+              l_run *= alpha;
+              sum_a *= alpha;
+#pragma unroll
+              for (int c = 0; c < 4; ++c) {
+                uint32_t r[32];
+                ptx::tmem_ld32(tO + c * 32, r);
+                ptx::tc_wait_ld();
+#pragma unroll
+                for (int e = 0; e < 32; ++e) r[e] = __float_as_uint(__uint_as_float(r[e]) * alpha);
+                ptx::tmem_st32(tO + c * 32, r);
+              }
+              ptx::tc_wait_st();
+            }
+            m_ref = m_new;
+          }
+          if (h == 0) sum_a = sum_h; else l_run += sum_a + sum_h;
+          ptx::tmem_st32(tS + h * 32, ph);         // S columns [0,64) were consumed by the first half
+          ptx::tc_wait_st();
+          ptx::tc_fence_before();
+          __syncwarp();
+          if (lane == 0 && kDbg != 2) ptx::mbar_arrive(bar((h == 0 ? bPReady : bP1Ready) + g));
+        }
+        continue;
+      }
       uint32_t pk[64];             // the row's 128 probabilities as bf16 pairs
       float mx;                    // row max of the raw scores of this tile
       uint64_t sum2;               // two partial row sums
@@ -543,7 +658,7 @@ bool tail_tc_supported(int Hq, int Hkv, float scale_log2) {
 // p.tail_bm = tail_tc_block_m(), p.last_tiles / p.nsplit_max from the plan.
 int launch_attn_tail_tc(const AttnParams& p, cudaStream_t s) {
   const int G = p.Hq / p.Hkv, P = G / 2, TT = kBM / P;
-  auto kern = attn_sm100_v3_kernel<4, 0, true>;
+  auto kern = attn_sm100_v3_kernel<4, 0, true, false>;
   static bool attr_set = false;
   if (!attr_set) {
     TMX_CUDA_TRY(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, kSmem));
@@ -573,11 +688,19 @@ int launch_attn_sm100_v3(const AttnParams& p, int variant, cudaStream_t s) {
   const int emu = variant & 3, dbg = (variant >> 2) & 3;
   using Kern = void (*)(const AttnParams, const TmaMaps);
   static const Kern table[4][4] = {
-      {attn_sm100_v3_kernel<4, 0, false>, attn_sm100_v3_kernel<0, 0, false>, attn_sm100_v3_kernel<6, 0, false>, attn_sm100_v3_kernel<8, 0, false>},
-      {attn_sm100_v3_kernel<0, 1, false>, attn_sm100_v3_kernel<0, 1, false>, attn_sm100_v3_kernel<0, 1, false>, attn_sm100_v3_kernel<0, 1, false>},
-      {attn_sm100_v3_kernel<0, 2, false>, attn_sm100_v3_kernel<4, 2, false>, attn_sm100_v3_kernel<6, 2, false>, attn_sm100_v3_kernel<8, 2, false>},
-      {attn_sm100_v3_kernel<0, 3, false>, attn_sm100_v3_kernel<4, 3, false>, attn_sm100_v3_kernel<6, 3, false>, attn_sm100_v3_kernel<8, 3, false>}};
+      {attn_sm100_v3_kernel<4, 0, false, false>, attn_sm100_v3_kernel<0, 0, false, false>, attn_sm100_v3_kernel<6, 0, false, false>, attn_sm100_v3_kernel<8, 0, false, false>},
+      {attn_sm100_v3_kernel<0, 1, false, false>, attn_sm100_v3_kernel<0, 1, false, false>, attn_sm100_v3_kernel<0, 1, false, false>, attn_sm100_v3_kernel<0, 1, false, false>},
+      {attn_sm100_v3_kernel<0, 2, false, false>, attn_sm100_v3_kernel<4, 2, false, false>, attn_sm100_v3_kernel<6, 2, false, false>, attn_sm100_v3_kernel<8, 2, false, false>},
+      {attn_sm100_v3_kernel<0, 3, false, false>, attn_sm100_v3_kernel<4, 3, false, false>, attn_sm100_v3_kernel<6, 3, false, false>, attn_sm100_v3_kernel<8, 3, false, false>}};
   Kern kern = table[dbg][emu];
+  // TMX_SM100_VARIANT bit 4: P stored in two halves with early PV issue (kSplitP).  Parity-green but
+  // measured SLOWER than the single store (1133 vs 1171 TFLOP/s at 32K, 1074 vs 1111 at 128K): the
+  // second store/fence/arrive and the lost TMEM-load overlap cost more than half a PV saves.
+  if (dbg == 0 && (variant & 16)) {
+    static const Kern split[4] = {attn_sm100_v3_kernel<4, 0, false, true>, attn_sm100_v3_kernel<0, 0, false, true>,
+                                  attn_sm100_v3_kernel<6, 0, false, true>, attn_sm100_v3_kernel<8, 0, false, true>};
+    kern = split[emu];
+  }
   TMX_CUDA_TRY(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, kSmem));
   TmaMaps maps;
   int st = tma_map_2d(&maps.q, p.q, p.total_T, (long long)p.Hq * kD, p.q_stride, kBM);
