@@ -202,7 +202,9 @@ extern "C" int tmx_prefill_attn(void* out, const void* q, const void* k, const v
     st = build_slots(reinterpret_cast<SlotInfo*>(ws + pl.off_slots), pl.n_slots, cu_seqlens, B,
                      max_seqlen, pl.stream_bm, pl.bn, si, sl, last, mode, s);
     if (st != TMX_OK) return st;
-    st = launch_attn_stream(p, s);
+    // TMX_SM100_VARIANT bit 5: the one-CTA-per-tile streaming kernel (v1) instead of the persistent one
+    st = (sm100_variant() & 32) ? launch_attn_stream(p, s) : launch_attn_stream2(p, s);
+    if (st == TMX_ERR_UNSUPPORTED) st = launch_attn_stream(p, s);
     if (st != TMX_OK || last <= 1 || pl.last_tiles == 0) return st;
     if (pl.tail_tc) return launch_attn_tail_tc(p, s);
     p.tail_only = 1;

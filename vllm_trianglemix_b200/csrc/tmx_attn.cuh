@@ -31,7 +31,8 @@ int launch_attn_mma(const AttnParams& p, int bm, cudaStream_t s);
 // streaming part of triangle layers (tmx_attn_stream.cu)
 bool stream_supported(int Hq, int Hkv, int si, int sl);
 int stream_block_m(int Hq, int Hkv);
-int launch_attn_stream(const AttnParams& p, cudaStream_t s);
+int launch_attn_stream(const AttnParams& p, cudaStream_t s);    // one CTA per tile (v1)
+int launch_attn_stream2(const AttnParams& p, cudaStream_t s);   // persistent, pipelined (default)
 int launch_attn_sm100(const AttnParams& p, int variant, cudaStream_t s);      // 64-key tiles (v2)
 int launch_attn_sm100_v3(const AttnParams& p, int variant, cudaStream_t s);   // 128-key tiles (v3, default)
 // dense tail rows of triangle layers on the tensor cores (split-KV + merge, tmx_attn_sm100_v3.cu)
