@@ -146,6 +146,41 @@ int tmx_prefill_attn(void* out, const void* q, const void* k, const void* v,
                      float* lse, void* workspace, size_t workspace_bytes, int kernel,
                      tmx_stream_t stream);
 
+/* ---- the step in front of attention -------------------
+ * One HBM pass over q/k(/v): per-head RMSNorm of q and k (weight [D], fp32 variance),
+ * NeoX rotary embedding from cos_sin_cache[positions[t]] ([max_pos, D] bf16: cos | sin),
+ * and, when k_cache/v_cache are given, the write of the new K (normed + rotated) and V
+ * rows into the paged cache at slot_mapping[t] (slot < 0 = padding token, skipped).
+ * Replaces Qwen3Attention.forward's q_norm / k_norm / rotary_emb calls
+ * (vllm/model_executor/models/qwen3.py:166-174) and reshape_and_cache_flash
+ * (vllm/v1/attention/backends/flash_attn.py:498-507; csrc/cache_kernels.cu) with the
+ * rounding order of the reference's forward_native methods
+ * (vllm/model_executor/layers/layernorm.py:170-206,
+ *  vllm/model_executor/layers/rotary_embedding/base.py:66-95, common.py:29-47).
+ * q [T, Hq*D], k/v [T, Hkv*D] bf16, token strides in elements; q_out/k_out may alias q/k.
+ * Cache layout: element (block, offset, head, d) at
+ *   block*cache_block_stride + offset*cache_token_stride + head*cache_head_stride + d
+ * (covers FlashAttention's [2, num_blocks, block_size, Hkv, D] NHD layout,
+ * flash_attn.py:78-87, and the HND permutation), bf16 cache only ("auto" kv_cache_dtype).
+ * D must be 128; all strides multiples of 4 elements, pointers 8-byte aligned.
+ * v / k_cache / v_cache / slot_mapping may all be null (no cache write). */
+int tmx_qk_norm_rope(void* q_out, void* k_out, const void* q, const void* k,
+                     const void* q_weight, const void* k_weight, const int64_t* positions,
+                     const void* cos_sin_cache, int max_pos, int T, int Hq, int Hkv, int D,
+                     int64_t q_stride_t, int64_t k_stride_t, int64_t qo_stride_t,
+                     int64_t ko_stride_t, float eps, const void* v, int64_t v_stride_t,
+                     void* k_cache, void* v_cache, const int64_t* slot_mapping,
+                     int64_t cache_block_stride, int64_t cache_token_stride,
+                     int64_t cache_head_stride, int block_size, tmx_stream_t stream);
+
+/* The cache write alone (key/value already final): ops.reshape_and_cache_flash
+ * (vllm/_custom_ops.py reshape_and_cache_flash -> csrc/cache_kernels.cu), bf16 cache. */
+int tmx_reshape_and_cache_flash(const void* key, const void* value, void* k_cache, void* v_cache,
+                                const int64_t* slot_mapping, int T, int Hkv, int D,
+                                int64_t k_stride_t, int64_t v_stride_t,
+                                int64_t cache_block_stride, int64_t cache_token_stride,
+                                int64_t cache_head_stride, int block_size, tmx_stream_t stream);
+
 /* Number of kernels the last tmx_prefill_attn call on this thread enqueued
  * (bench.py's gpu_launches accounting). */
 int tmx_last_launch_count(void);

@@ -41,7 +41,7 @@ def u16(t):
 def main():
     torch.manual_seed(0)
     out = {}
-    for tag, (t, hq, hkv, max_pos) in {"a": (37, 4, 2, 4096), "b": (256, 16, 8, 40960)}.items():
+    for tag, (t, hq, hkv, max_pos) in {"a": (37, 4, 2, 4096), "b": (64, 8, 2, 40960)}.items():
         d = 128
         qw = (1.0 + 0.1 * torch.randn(d)).bfloat16()
         kw = (1.0 + 0.1 * torch.randn(d)).bfloat16()

@@ -1,0 +1,210 @@
+"""GPU parity of the step in front of attention: fused q/k RMSNorm +
+NeoX RoPE (+ KV-cache write) through the C ABI against the oracle and the reference-produced
+golden vectors.
+
+Tolerance (stated, floating point): every operation of the reference's forward_native is
+reproduced with its bf16 rounding, so the only freedom is the fp32 summation order of the 128
+squares in the variance.  That can move rsqrt by 1 fp32 ulp, which flips a bf16 rounding for
+about 1 element in 2^8..2^16; such a flip is 1 bf16 ulp and RoPE's two rounded products can carry
+it to 2 ulp of the larger operand.  Bar: >= 99.5 % of elements bit-identical, the rest within
+atol 1.5e-2 / rtol 1e-2 (the attention bar) of the oracle.  Cache rows and untouched slots:
+bit-exact."""
+import os
+
+import numpy as np
+import pytest
+import torch
+
+from oracle import qknorm_rope_oracle as orc
+from oracle import trianglemix_oracle as aorc
+
+pytestmark = pytest.mark.gpu
+DEV = "cuda:0"
+G = np.load(os.path.join(os.path.dirname(__file__), "golden", "qknorm_rope.npz"))
+
+
+@pytest.fixture(scope="module")
+def ops():
+    from vllm_trianglemix_b200 import ops as o
+    return o
+
+
+@pytest.fixture(scope="module")
+def tmx():
+    import vllm_trianglemix_b200 as m
+    return m
+
+
+def bf(a):
+    return torch.from_numpy(a.copy()).view(torch.bfloat16)
+
+
+def close_enough(got, want, what):
+    got, want = got.cpu(), want.cpu()
+    same = (got.view(torch.int16) == want.view(torch.int16)).float().mean().item()
+    assert same >= 0.995, "%s: only %.4f of elements bit-identical" % (what, same)
+    g, w = got.float(), want.float()
+    bad = ((g - w).abs() > 1.5e-2 + 1e-2 * w.abs()).sum().item()
+    assert bad == 0, "%s: %d elements outside tolerance (max abs %.3e)" % (what, bad, (g - w).abs().max().item())
+    return same
+
+
+@pytest.mark.parametrize("tag", ["a", "b"])
+def test_golden_from_reference(ops, tag):
+    t, hq, hkv, d, max_pos = (int(x) for x in G[tag + "_params"])
+    cache = orc.cos_sin_cache(d, max_pos, 1000000.0)
+    pos = torch.from_numpy(G[tag + "_pos"])
+    q2, k2 = ops.qk_norm_rope(pos.to(DEV), bf(G[tag + "_q"]).to(DEV), bf(G[tag + "_k"]).to(DEV),
+                              bf(G[tag + "_qw"]).to(DEV), bf(G[tag + "_kw"]).to(DEV), cache.to(DEV), 1e-6, d)
+    close_enough(q2, bf(G[tag + "_qo"]), "q")
+    close_enough(k2, bf(G[tag + "_ko"]), "k")
+    assert ops.last_launch_count() == 1
+
+
+def _inputs(t, hq, hkv, max_pos, seed, qscale=3.0):
+    g = torch.Generator().manual_seed(seed)
+    d = 128
+    qkv = torch.randn(t, (hq + 2 * hkv) * d, generator=g)
+    qkv[:, :hq * d] *= qscale
+    qkv = qkv.bfloat16()
+    qw = (1.0 + 0.1 * torch.randn(d, generator=g)).bfloat16()
+    kw = (1.0 + 0.1 * torch.randn(d, generator=g)).bfloat16()
+    pos = torch.randint(0, max_pos, (t,), generator=g, dtype=torch.int64)
+    return qkv, qw, kw, pos
+
+
+@pytest.mark.parametrize("t,hq,hkv", [(1, 2, 1), (37, 4, 2), (1000, 16, 8), (4099, 32, 8), (513, 8, 1)])
+@pytest.mark.parametrize("inplace", [False, True])
+def test_vs_oracle_packed_qkv_views(ops, t, hq, hkv, inplace):
+    """q/k are strided views of the packed qkv buffer, as qkv.split gives them (qwen3.py:161)."""
+    d, max_pos = 128, 8192
+    qkv, qw, kw, pos = _inputs(t, hq, hkv, max_pos, seed=t)
+    cache = orc.cos_sin_cache(d, max_pos, 10000.0)
+    q, k, v = qkv.split([hq * d, hkv * d, hkv * d], dim=-1)
+    wq, wk = orc.qk_norm_rope(q, k, pos, qw, kw, cache, 1e-6, d)
+    qkv_d = qkv.to(DEV)
+    qd, kd, vd = qkv_d.split([hq * d, hkv * d, hkv * d], dim=-1)
+    gq, gk = ops.qk_norm_rope(pos.to(DEV), qd, kd, qw.to(DEV), kw.to(DEV), cache.to(DEV), 1e-6, d, inplace=inplace)
+    torch.cuda.synchronize()
+    close_enough(gq, wq, "q")
+    close_enough(gk, wk, "k")
+    assert torch.equal(vd.cpu(), v)                                  # v untouched
+    if inplace:
+        assert gq.data_ptr() == qd.data_ptr() and gk.data_ptr() == kd.data_ptr()
+    else:
+        assert torch.equal(qd.cpu(), q) and torch.equal(kd.cpu(), k)  # inputs untouched
+
+
+def test_empty_and_bad_arguments(ops):
+    from vllm_trianglemix_b200 import TmxError
+    d = 128
+    cache = orc.cos_sin_cache(d, 16, 10000.0).to(DEV)
+    w = torch.ones(d, dtype=torch.bfloat16, device=DEV)
+    q0 = torch.empty(0, 4 * d, dtype=torch.bfloat16, device=DEV)
+    k0 = torch.empty(0, 2 * d, dtype=torch.bfloat16, device=DEV)
+    gq, gk = ops.qk_norm_rope(torch.empty(0, dtype=torch.int64, device=DEV), q0, k0, w, w, cache, 1e-6)
+    assert gq.shape == q0.shape and gk.shape == k0.shape
+    q = torch.zeros(3, 4 * d, dtype=torch.bfloat16, device=DEV)
+    k = torch.zeros(3, 2 * d, dtype=torch.bfloat16, device=DEV)
+    pos = torch.zeros(3, dtype=torch.int64, device=DEV)
+    with pytest.raises(TmxError):
+        ops.qk_norm_rope(pos, q.float(), k, w, w, cache, 1e-6)           # dtype
+    with pytest.raises(TmxError):
+        ops.qk_norm_rope(pos[:2], q, k, w, w, cache, 1e-6)               # positions length
+    with pytest.raises(TmxError):
+        ops.qk_norm_rope(pos, q[:, :64 * 7], k, w, w, cache, 1e-6)       # not a multiple of head_dim
+    with pytest.raises(TmxError):
+        ops.qk_norm_rope(pos, q.cpu(), k.cpu(), w.cpu(), w.cpu(), cache.cpu(), 1e-6)   # no CPU path
+    # all-zero rows: rsqrt(eps) * 0 = 0, no NaN
+    gq, gk = ops.qk_norm_rope(pos, q, k, w, w, cache, 1e-6)
+    assert not gq.float().abs().sum().item() and not gk.float().abs().sum().item()
+
+
+@pytest.mark.parametrize("layout", ["NHD", "HND"])
+@pytest.mark.parametrize("t,hkv,block_size,num_blocks", [(42, 8, 16, 8), (1, 1, 16, 1), (777, 2, 32, 40)])
+def test_reshape_and_cache_flash_vs_reference_loop(ops, layout, t, hkv, block_size, num_blocks):
+    """Mirrors the reference's own test (tests/kernels/attention/test_cache.py:230-370):
+    random unique slots, key/value as views of a packed qkv tensor, both cache layouts."""
+    g = torch.Generator().manual_seed(t)
+    d = 128
+    qkv = torch.randn(t, 3, hkv, d, generator=g).bfloat16()
+    _, key, value = qkv.unbind(dim=1)
+    slots = torch.randperm(block_size * num_blocks, generator=g)[:t].to(torch.int64)
+    if t > 4:
+        slots[3] = -1                                                    # a padding token
+    shape = (2, num_blocks, block_size, hkv, d) if layout == "NHD" else (2, num_blocks, hkv, block_size, d)
+    kv = torch.randn(shape, generator=g).bfloat16()
+    want = kv.clone()
+    wk, wv = want.unbind(0)
+    if layout == "HND":
+        wk, wv = wk.permute(0, 2, 1, 3), wv.permute(0, 2, 1, 3)
+    orc.reshape_and_cache_flash(key, value, wk, wv, slots)
+    kv_d = kv.to(DEV)
+    kc, vc = kv_d.unbind(0)
+    if layout == "HND":
+        kc, vc = kc.permute(0, 2, 1, 3), vc.permute(0, 2, 1, 3)
+    qkv_d = qkv.to(DEV)
+    _, key_d, value_d = qkv_d.unbind(dim=1)
+    ops.reshape_and_cache_flash(key_d, value_d, kc, vc, slots.to(DEV), "auto", None, None)
+    torch.cuda.synchronize()
+    assert torch.equal(kv_d.cpu(), want)
+    from vllm_trianglemix_b200 import TmxError
+    with pytest.raises(TmxError):
+        ops.reshape_and_cache_flash(key_d, value_d, kc, vc, slots.to(DEV), "fp8", None, None)
+
+
+def test_fused_cache_write_matches_separate_steps(ops):
+    """norm+rope+cache in one launch == norm+rope, then the cache write of its k and the raw v."""
+    t, hq, hkv, d, max_pos, bs, nb = 2500, 32, 8, 128, 40960, 16, 200
+    qkv, qw, kw, pos = _inputs(t, hq, hkv, max_pos, seed=7)
+    cache = orc.cos_sin_cache(d, max_pos, 1000000.0).to(DEV)
+    g = torch.Generator().manual_seed(8)
+    slots = torch.randperm(bs * nb, generator=g)[:t].to(torch.int64)
+    slots[5] = -1
+    a = qkv.to(DEV)
+    qa, ka, va = a.split([hq * d, hkv * d, hkv * d], dim=-1)
+    kv1 = torch.zeros(2, nb, bs, hkv, d, dtype=torch.bfloat16, device=DEV)
+    kv2 = torch.zeros_like(kv1)
+    args = (pos.to(DEV), qa, ka, qw.to(DEV), kw.to(DEV), cache, 1e-6, d)
+    q1, k1 = ops.qk_norm_rope(*args, v=va, key_cache=kv1[0], value_cache=kv1[1], slot_mapping=slots.to(DEV))
+    assert ops.last_launch_count() == 1
+    q2, k2 = ops.qk_norm_rope(*args)
+    ops.reshape_and_cache_flash(k2.view(t, hkv, d), va.view(t, hkv, d), kv2[0], kv2[1], slots.to(DEV))
+    torch.cuda.synchronize()
+    assert torch.equal(q1, q2) and torch.equal(k1, k2) and torch.equal(kv1, kv2)
+    # and against the oracle: cache rows hold exactly the k the kernel returned and the raw v
+    wkc = torch.zeros(nb, bs, hkv, d, dtype=torch.bfloat16)
+    wvc = torch.zeros_like(wkc)
+    orc.reshape_and_cache_flash(k1.cpu().view(t, hkv, d), qkv[:, (hq + hkv) * d:].reshape(t, hkv, d), wkc, wvc, slots)
+    assert torch.equal(kv1[0].cpu(), wkc) and torch.equal(kv1[1].cpu(), wvc)
+
+
+@pytest.mark.parametrize("layer_idx", [0, 1])
+def test_qwen3_block_end_to_end(tmx, layer_idx):
+    """Qwen3Attention.forward between the projections (qwen3.py:160-190), hook wired: packed qkv in,
+    attn_output out, against oracle prologue -> oracle masked attention; KV cache rows written."""
+    t, hq, hkv, d, max_pos = 3000, 8, 2, 128, 4096
+    si, sl, last = 4, 32, 64
+    qkv, qw, kw, _ = _inputs(t, hq, hkv, max_pos, seed=11, qscale=1.0)
+    pos = torch.arange(t, dtype=torch.int64)
+    cfg = tmx.TriangleMixConfig(si, sl, last, triangle_layer_indices=[1])
+    blk = tmx.Qwen3TriangleMixAttention(hq, hkv, d, max_position=max_pos, rms_norm_eps=1e-6, rope_theta=1000000.0,
+                                        trianglemix_config=cfg, layer_idx=layer_idx, num_layers=2, device=DEV)
+    blk.q_norm_weight.data.copy_(qw)
+    blk.k_norm_weight.data.copy_(kw)
+    assert torch.equal(blk.cos_sin_cache.cpu(), orc.cos_sin_cache(d, max_pos, 1000000.0))
+    meta = tmx.TriangleMixMetadataBuilder.from_seq_lens([t], DEV)
+    bs, nb = 16, (t + 15) // 16
+    meta.slot_mapping = torch.arange(t, dtype=torch.int64, device=DEV)
+    kv_cache = torch.zeros(tmx.TriangleMixBackend.get_kv_cache_shape(nb, bs, hkv, d), dtype=torch.bfloat16, device=DEV)
+    out = blk(pos.to(DEV), qkv.to(DEV), kv_cache, meta)
+    torch.cuda.synchronize()
+    q, k, v = qkv.split([hq * d, hkv * d, hkv * d], dim=-1)
+    wq, wk = orc.qk_norm_rope(q, k, pos, qw, kw, orc.cos_sin_cache(d, max_pos, 1000000.0), 1e-6, d)
+    mode = aorc.TRIANGLE if layer_idx == 1 else aorc.DENSE_CAUSAL
+    ref = aorc.attention_varlen_fp32(wq.view(t, hq, d), wk.view(t, hkv, d), v.reshape(t, hkv, d), [0, t], d ** -0.5,
+                                     si, sl, last, mode)
+    rep = aorc.error_report(out.cpu().view(t, hq, d), ref)
+    assert rep["violations"] == 0, rep
+    close_enough(kv_cache[0].view(-1, hkv * d)[:t], wk, "k cache")
+    assert torch.equal(kv_cache[1].view(-1, hkv * d)[:t].cpu(), v)

@@ -12,8 +12,9 @@ ChunkedLocalAttention / EncoderOnlyAttention install theirs:
 
 The classes are duck-typed (no ``import vllm``: the vllm wheel in this image is an
 unrelated upstream release).  Prefill only: K/V of the call are the whole
-context, as in ``_forward_encoder_attention`` (flash_attn.py:578-633); ``kv_cache``
-is ignored.  TriangleMix parameters and ``layer_idx`` travel as extra impl kwargs,
+context, as in ``_forward_encoder_attention`` (flash_attn.py:578-633); a ``kv_cache``
+is written (new K/V rows at ``attn_metadata.slot_mapping``, flash_attn.py:483-507) but
+never read.  TriangleMix parameters and ``layer_idx`` travel as extra impl kwargs,
 the way ``dual_chunk_attention_config`` + ``layer_idx`` do in the reference's
 vllm/model_executor/models/qwen3.py:150-153.
 """
@@ -39,6 +40,7 @@ class TriangleMixMetadata:
     seq_lens: Optional[torch.Tensor] = None
     causal: bool = True
     query_start_loc_cpu: Optional[torch.Tensor] = None
+    slot_mapping: Optional[torch.Tensor] = None   # int64 [num_actual_tokens], flash_attn.py:127
 
 
 class TriangleMixMetadataBuilder:
@@ -54,7 +56,8 @@ class TriangleMixMetadataBuilder:
             num_actual_tokens=int(m.num_actual_tokens), max_query_len=int(m.max_query_len),
             query_start_loc=m.query_start_loc, max_seq_len=int(getattr(m, "max_seq_len", m.max_query_len)),
             seq_lens=getattr(m, "seq_lens", None), causal=getattr(m, "causal", True),
-            query_start_loc_cpu=getattr(m, "query_start_loc_cpu", None))
+            query_start_loc_cpu=getattr(m, "query_start_loc_cpu", None),
+            slot_mapping=getattr(m, "slot_mapping", None))
 
     @staticmethod
     def from_seq_lens(seq_lens: List[int], device) -> TriangleMixMetadata:
@@ -146,6 +149,11 @@ class TriangleMixImpl:
         k = key[:t].view(t, self.num_kv_heads, self.head_size)
         v = value[:t].view(t, self.num_kv_heads, self.head_size)
         out = output[:t].view(t, self.num_heads, self.head_size)
+        slot_mapping = getattr(attn_metadata, "slot_mapping", None)
+        if kv_cache is not None and kv_cache.numel() > 0 and slot_mapping is not None:
+            # store the new K/V rows in the paged cache (flash_attn.py:483-507)
+            key_cache, value_cache = kv_cache.unbind(0)
+            ops.reshape_and_cache_flash(k, v, key_cache, value_cache, slot_mapping, self.kv_cache_dtype)
         mode, si, sl, last = self.mask_mode()
         ops.prefill_attn(q, k, v, attn_metadata.query_start_loc, attn_metadata.max_query_len, self.scale,
                          si, sl, last, mode, out=out, kernel=self.kernel)

@@ -189,5 +189,104 @@ def prefill_attn(q: torch.Tensor, k: torch.Tensor, v: torch.Tensor, cu_seqlens: 
     return (out, lse) if return_lse else out
 
 
+def _cache_strides(key_cache: torch.Tensor, value_cache: torch.Tensor):
+    """(block, token, head) element strides of a [num_blocks, block_size, Hkv, D] cache view
+    (NHD as FlashAttention allocates it, flash_attn.py:78-87, or an HND-permuted view)."""
+    if key_cache.dim() != 4 or key_cache.shape != value_cache.shape or key_cache.stride() != value_cache.stride():
+        raise _lib.TmxError("key_cache / value_cache must be [num_blocks, block_size, Hkv, D] views with equal "
+                            "strides; got %r %r" % (tuple(key_cache.shape), tuple(value_cache.shape)))
+    if key_cache.dtype != torch.bfloat16 or value_cache.dtype != torch.bfloat16:
+        raise _lib.TmxError("only a bfloat16 KV cache (kv_cache_dtype='auto') is supported, got %s" % key_cache.dtype)
+    if key_cache.stride(3) != 1:
+        raise _lib.TmxError("KV cache head_dim must be contiguous")
+    return key_cache.stride(0), key_cache.stride(1), key_cache.stride(2), key_cache.shape[1]
+
+
+def _slots(slot_mapping: torch.Tensor) -> torch.Tensor:
+    if slot_mapping.dtype != torch.int64 or not slot_mapping.is_contiguous():
+        slot_mapping = slot_mapping.to(torch.int64).contiguous()
+    return slot_mapping
+
+
+def reshape_and_cache_flash(key: torch.Tensor, value: torch.Tensor, key_cache: torch.Tensor,
+                            value_cache: torch.Tensor, slot_mapping: torch.Tensor, kv_cache_dtype: str = "auto",
+                            k_scale: Optional[torch.Tensor] = None, v_scale: Optional[torch.Tensor] = None) -> None:
+    """Same signature as the reference's ops.reshape_and_cache_flash (vllm/_custom_ops.py:1605-1618):
+    key/value [T, Hkv, D] -> cache rows at slot_mapping (len(slot_mapping) tokens, slot < 0 skipped).
+    bf16 cache only; the scales are accepted and unused, as in the reference's 'auto' path."""
+    device = _require_cuda(key.device)
+    lib = _lib.load()
+    if kv_cache_dtype not in ("auto", "bfloat16"):
+        raise _lib.TmxError("kv_cache_dtype %r is not supported (bf16 cache only)" % (kv_cache_dtype,))
+    if key.dtype != torch.bfloat16 or value.dtype != torch.bfloat16:
+        raise _lib.TmxError("reshape_and_cache_flash needs bfloat16 key/value")
+    if key.dim() != 3 or value.shape != key.shape or key.stride(2) != 1 or key.stride(1) != key.shape[2] \
+            or value.stride(2) != 1 or value.stride(1) != value.shape[2]:
+        raise _lib.TmxError("key/value must be [T, Hkv, D] with contiguous heads")
+    blk, tok, head, block_size = _cache_strides(key_cache, value_cache)
+    slots = _slots(slot_mapping)
+    t = min(slots.numel(), key.shape[0])           # slot_mapping's length = actual tokens (flash_attn.py:493-497)
+    with torch.cuda.device(device):
+        st = lib.tmx_reshape_and_cache_flash(key.data_ptr(), value.data_ptr(), key_cache.data_ptr(),
+                                             value_cache.data_ptr(), slots.data_ptr(), t, key.shape[1],
+                                             key.shape[2], key.stride(0), value.stride(0), blk, tok, head,
+                                             block_size, _stream(device))
+    _lib.check(st, "tmx_reshape_and_cache_flash")
+
+
+def qk_norm_rope(positions: torch.Tensor, q: torch.Tensor, k: torch.Tensor, q_weight: torch.Tensor,
+                 k_weight: torch.Tensor, cos_sin_cache: torch.Tensor, eps: float, head_dim: int = 128,
+                 inplace: bool = False, v: Optional[torch.Tensor] = None,
+                 key_cache: Optional[torch.Tensor] = None, value_cache: Optional[torch.Tensor] = None,
+                 slot_mapping: Optional[torch.Tensor] = None) -> Tuple[torch.Tensor, torch.Tensor]:
+    """Fused per-head q/k RMSNorm + NeoX RoPE (+ optional KV-cache write) -- one kernel for
+    qwen3.py:166-174 (+ flash_attn.py:498-507).  q [T, Hq*D], k [T, Hkv*D] bf16 (row-contiguous);
+    positions int64 [T]; cos_sin_cache [max_pos, D] bf16.  Returns (q, k) like rotary_emb does."""
+    device = _require_cuda(q.device)
+    lib = _lib.load()
+    for name, x in (("q", q), ("k", k), ("q_weight", q_weight), ("k_weight", k_weight), ("cos_sin_cache", cos_sin_cache)):
+        if x.dtype != torch.bfloat16:
+            raise _lib.TmxError("qk_norm_rope needs bfloat16 %s, got %s" % (name, x.dtype))
+    if q.dim() != 2 or k.dim() != 2 or q.shape[0] != k.shape[0] or q.shape[1] % head_dim or k.shape[1] % head_dim:
+        raise _lib.TmxError("expected q [T, Hq*D], k [T, Hkv*D]; got %r %r" % (tuple(q.shape), tuple(k.shape)))
+    if q.stride(1) != 1:
+        q = q.contiguous()
+    if k.stride(1) != 1:
+        k = k.contiguous()
+    t = q.shape[0]
+    hq, hkv = q.shape[1] // head_dim, k.shape[1] // head_dim
+    pos = positions.flatten()
+    if pos.dtype != torch.int64 or not pos.is_contiguous():
+        pos = pos.to(torch.int64).contiguous()
+    if pos.numel() != t:
+        raise _lib.TmxError("positions has %d entries for %d tokens" % (pos.numel(), t))
+    cache = cos_sin_cache if cos_sin_cache.is_contiguous() else cos_sin_cache.contiguous()
+    if cache.dim() != 2 or cache.shape[1] != head_dim:
+        raise _lib.TmxError("cos_sin_cache must be [max_pos, head_dim] (rotary_dim == head_dim)")
+    q_out = q if inplace else torch.empty((t, hq * head_dim), dtype=torch.bfloat16, device=device)
+    k_out = k if inplace else torch.empty((t, hkv * head_dim), dtype=torch.bfloat16, device=device)
+    cargs = (None, 0, None, None, None, 0, 0, 0, 0)
+    if key_cache is not None:
+        if v is None or value_cache is None or slot_mapping is None:
+            raise _lib.TmxError("the fused cache write needs v, key_cache, value_cache and slot_mapping")
+        if v.dtype != torch.bfloat16 or v.shape != k.shape:
+            raise _lib.TmxError("v must be bf16 with k's shape")
+        if v.stride(1) != 1:
+            v = v.contiguous()
+        blk, tok, head, block_size = _cache_strides(key_cache, value_cache)
+        slots = _slots(slot_mapping)
+        if slots.numel() < t:                     # padded q/k beyond the actual tokens: no slot -> skip
+            slots = torch.cat([slots, slots.new_full((t - slots.numel(),), -1)])
+        cargs = (v.data_ptr(), v.stride(0), key_cache.data_ptr(), value_cache.data_ptr(), slots.data_ptr(),
+                 blk, tok, head, block_size)
+    with torch.cuda.device(device):
+        st = lib.tmx_qk_norm_rope(q_out.data_ptr(), k_out.data_ptr(), q.data_ptr(), k.data_ptr(),
+                                  q_weight.data_ptr(), k_weight.data_ptr(), pos.data_ptr(), cache.data_ptr(),
+                                  cache.shape[0], t, hq, hkv, head_dim, q.stride(0), k.stride(0),
+                                  q_out.stride(0), k_out.stride(0), float(eps), *cargs, _stream(device))
+    _lib.check(st, "tmx_qk_norm_rope")
+    return q_out, k_out
+
+
 def last_launch_count() -> int:
     return _lib.load().tmx_last_launch_count()
