@@ -162,7 +162,7 @@ int tmx_prefill_attn(void* out, const void* q, const void* k, const void* v,
  *   block*cache_block_stride + offset*cache_token_stride + head*cache_head_stride + d
  * (covers FlashAttention's [2, num_blocks, block_size, Hkv, D] NHD layout,
  * flash_attn.py:78-87, and the HND permutation), bf16 cache only ("auto" kv_cache_dtype).
- * D must be 128; all strides multiples of 4 elements, pointers 8-byte aligned.
+ * D must be 128; all strides multiples of 8 elements, pointers 16-byte aligned.
  * v / k_cache / v_cache / slot_mapping may all be null (no cache write). */
 int tmx_qk_norm_rope(void* q_out, void* k_out, const void* q, const void* k,
                      const void* q_weight, const void* k_weight, const int64_t* positions,

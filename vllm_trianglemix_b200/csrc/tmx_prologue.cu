@@ -7,12 +7,15 @@
 //   vllm/v1/attention/backends/flash_attn.py:498-507                 (reshape_and_cache_flash)
 // HBM-bound, no reuse: q/k are read once and written once, v is read once and written once into
 // the cache, the normed+rotated k goes to both the contiguous tensor the attention kernel reads
-// and the cache.  Work unit = one (token, head) row of 128 bf16 = 256 B, served by a HALF-WARP:
-// lane l holds elements [4l, 4l+4) and [64+4l, 64+4l+4) (two 8-byte accesses, each a fully used
-// 128-byte line per half-warp), so both members of every rotary pair (e, e+64) sit in the same
-// lane and the only exchange is the 4-step sum-of-squares butterfly.  Two units are in flight
-// per half-warp per iteration (loads of both issued before either is used) and the grid is a
-// multiple of the SM count.
+// and the cache.  One WARP per token (grid-stride): position, slot and the token's cos/sin row are
+// fetched once and reused by all of its heads.  A head row (128 bf16 = 256 B) is served by a
+// QUARTER-WARP: lane l8 holds elements [8*l8, 8*l8+8) and [64+8*l8, 64+8*l8+8) -- two 16-byte
+// accesses, each a fully used 128-byte line per quarter-warp -- so both members of every rotary
+// pair (e, e+64) sit in the same lane and the only exchange is a 3-step sum-of-squares butterfly.
+// A warp covers 4 heads per pass and keeps two passes of loads in flight.  (First version: a
+// half-warp per head with 8-byte accesses and a per-row decode ran at 70 % issue utilisation,
+// 390 instructions per 4 rows -- profiles/r01_prologue_experiments.md.)
+#include <cstdlib>
 #include "tmx_common.cuh"
 
 namespace tmx {
@@ -20,8 +23,9 @@ namespace {
 
 constexpr int kD = 128;
 constexpr int kThreads = 256;
-constexpr int kHalfWarpsPerCta = kThreads / 16;
+constexpr int kWarpsPerCta = kThreads / 32;
 constexpr int kUnroll = 2;
+constexpr int kMinCtasPerSm = 3;        // <= 80 registers, no spills: 768 threads per SM, 64 B in flight each
 
 struct PrologueParams {
   const __nv_bfloat16 *q, *k, *v;
@@ -33,149 +37,191 @@ struct PrologueParams {
   const long long* slots;
   long long q_st, k_st, v_st, qo_st, ko_st;
   long long blk_st, tok_st, head_st;  // cache strides (elements)
-  long long units;                    // T * units_per_token
-  int T, Hq, Hkv, upt, block_size, max_pos;
+  int T, Hq, Hkv, block_size, max_pos;
   int norm_rope;                      // 0: cache write only
+  int bs_shift;                       // log2(block_size) when it is a power of two, else -1
   float eps;
 };
 
+__device__ __forceinline__ uint4 ld16(const __nv_bfloat16* p) {
+  return __ldg(reinterpret_cast<const uint4*>(p));
+}
+__device__ __forceinline__ uint4 ld16_stream(const __nv_bfloat16* p) {  // read-once data: keep it out of L1
+  uint4 r;
+  asm volatile("ld.global.L1::no_allocate.v4.u32 {%0, %1, %2, %3}, [%4];"
+               : "=r"(r.x), "=r"(r.y), "=r"(r.z), "=r"(r.w) : "l"(p));
+  return r;
+}
+__device__ __forceinline__ void st16(__nv_bfloat16* p, uint4 v) { *reinterpret_cast<uint4*>(p) = v; }
+
+// ---- arithmetic in the reference's rounding order without the conversion (XU) pipe --------
+// The reference rounds to bf16 after every torch op.  For two bf16 operands the fp32 product is
+// exact, and the fp32 sum/difference is either exact or differs from the exact value by less than
+// the bf16 rounding could see, so "fp32 op, then round to bf16" == the single-rounded native
+// bf16x2 instruction (mul.rn.bf16x2 / add.rn.bf16x2 / sub.rn.bf16x2).  Only x * rsqrt(var) has an
+// fp32 operand; that one is an FMUL followed by the packed cvt.rn.bf16x2.f32.
+__device__ __forceinline__ float lo_f(uint32_t w) { return __uint_as_float(w << 16); }
+__device__ __forceinline__ float hi_f(uint32_t w) { return __uint_as_float(w & 0xffff0000u); }
+__device__ __forceinline__ uint32_t pack_rn(float lo, float hi) {
+  uint32_t r;
+  asm("cvt.rn.bf16x2.f32 %0, %1, %2;" : "=r"(r) : "f"(hi), "f"(lo));
+  return r;
+}
+__device__ __forceinline__ uint32_t mul2(uint32_t a, uint32_t b) {
+  uint32_t r;
+  asm("mul.rn.bf16x2 %0, %1, %2;" : "=r"(r) : "r"(a), "r"(b));
+  return r;
+}
+__device__ __forceinline__ uint32_t add2(uint32_t a, uint32_t b) {
+  uint32_t r;
+  asm("add.rn.bf16x2 %0, %1, %2;" : "=r"(r) : "r"(a), "r"(b));
+  return r;
+}
+__device__ __forceinline__ uint32_t sub2(uint32_t a, uint32_t b) {
+  uint32_t r;
+  asm("sub.rn.bf16x2 %0, %1, %2;" : "=r"(r) : "r"(a), "r"(b));
+  return r;
+}
+
 struct Row {
-  uint2 a, b;  // elements [4l,4l+4) and [64+4l, 64+4l+4)
+  uint4 a, b;  // elements [8*l8, 8*l8+8) and [64+8*l8, 64+8*l8+8)
 };
 
-__device__ __forceinline__ uint2 ld8(const __nv_bfloat16* p) {
-  return __ldg(reinterpret_cast<const uint2*>(p));
-}
-__device__ __forceinline__ uint2 ld8_stream(const __nv_bfloat16* p) {  // read-once data: keep it out of L1
-  uint2 r;
-  asm volatile("ld.global.L1::no_allocate.v2.u32 {%0, %1}, [%2];" : "=r"(r.x), "=r"(r.y) : "l"(p));
-  return r;
-}
-__device__ __forceinline__ void st8(__nv_bfloat16* p, uint2 v) { *reinterpret_cast<uint2*>(p) = v; }
-
-__device__ __forceinline__ void unpack4(uint2 r, float* f) {
-  f[0] = __uint_as_float(r.x << 16);
-  f[1] = __uint_as_float(r.x & 0xffff0000u);
-  f[2] = __uint_as_float(r.y << 16);
-  f[3] = __uint_as_float(r.y & 0xffff0000u);
-}
-// round-to-nearest-even to bf16 and back: "the torch op returned a bf16 tensor"
-__device__ __forceinline__ float rbf(float x) { return __bfloat162float(__float2bfloat16_rn(x)); }
-__device__ __forceinline__ uint2 pack4(const float* f) {  // f already bf16-representable
-  uint2 r;
-  r.x = (__float_as_uint(f[0]) >> 16) | (__float_as_uint(f[1]) & 0xffff0000u);
-  r.y = (__float_as_uint(f[2]) >> 16) | (__float_as_uint(f[3]) & 0xffff0000u);
-  return r;
-}
-
-struct Unit {
-  long long t;
-  int h;      // head inside its tensor
-  int kind;   // 0 q, 1 k, 2 v, -1 none
-};
-
-__device__ __forceinline__ Unit decode(const PrologueParams& p, long long u) {
-  Unit x;
-  if (u >= p.units) { x.t = 0; x.h = 0; x.kind = -1; return x; }
-  x.t = u / p.upt;
-  int r = (int)(u - x.t * p.upt);
-  if (r < p.Hq) { x.kind = 0; x.h = r; }
-  else if (r < p.Hq + p.Hkv) { x.kind = 1; x.h = r - p.Hq; }
-  else { x.kind = 2; x.h = r - p.Hq - p.Hkv; }
-  return x;
-}
-
-__global__ void __launch_bounds__(kThreads) prologue_kernel(const PrologueParams p) {
-  const int lane16 = threadIdx.x & 15;
-  const long long hw = (long long)blockIdx.x * kHalfWarpsPerCta + (threadIdx.x >> 4);
-  const long long stride = (long long)gridDim.x * kHalfWarpsPerCta;
-  const int e0 = 4 * lane16;
-
-  for (long long base = hw; base < p.units; base += stride * kUnroll) {
-    Unit un[kUnroll];
-    Row x[kUnroll];
-    uint2 cs[kUnroll][2];
-    long long slot[kUnroll];
+// RMSNorm + NeoX RoPE of one head row held across a quarter-warp (qmask names its 8 lanes).
+// wp -> this lane's 8 + 8 weight elements (L1-resident; not kept in registers across rows).
+__device__ __forceinline__ Row norm_rope_row(const Row& x, const __nv_bfloat16* wp, const uint4& cosv,
+                                             const uint4& sinv, float eps, unsigned qmask) {
+  const uint32_t xw[8] = {x.a.x, x.a.y, x.a.z, x.a.w, x.b.x, x.b.y, x.b.z, x.b.w};
+  float s0 = 0.f, s1 = 0.f;
 #pragma unroll
-    for (int i = 0; i < kUnroll; ++i) {
-      un[i] = decode(p, base + i * stride);
-      slot[i] = -1;
-      if (un[i].kind < 0) continue;
-      const __nv_bfloat16* src = un[i].kind == 0   ? p.q + un[i].t * p.q_st
-                                 : un[i].kind == 1 ? p.k + un[i].t * p.k_st
-                                                   : p.v + un[i].t * p.v_st;
-      src += (long long)un[i].h * kD + e0;
-      x[i].a = ld8_stream(src);
-      x[i].b = ld8_stream(src + 64);
-      if (un[i].kind != 2 && p.norm_rope) {
-        long long pos = p.pos[un[i].t];
-        const __nv_bfloat16* c = p.cache + pos * kD + e0;
-        cs[i][0] = ld8(c);        // cos[4l .. 4l+3]
-        cs[i][1] = ld8(c + 64);   // sin[4l .. 4l+3]
-      }
-      if (un[i].kind != 0 && p.slots) slot[i] = p.slots[un[i].t];
+  for (int e = 0; e < 8; ++e) {                         // bf16 squares are exact in fp32
+    const float lo = lo_f(xw[e]), hi = hi_f(xw[e]);
+    s0 = fmaf(lo, lo, s0);
+    s1 = fmaf(hi, hi, s1);
+  }
+  float ss = s0 + s1;
+#pragma unroll
+  for (int o = 4; o >= 1; o >>= 1) ss += __shfl_xor_sync(qmask, ss, o);
+  // torch.rsqrt on the CPU is 1 / sqrt(x), both correctly rounded; so are these
+  const float rs = __frcp_rn(__fsqrt_rn(ss * (1.0f / kD) + eps));
+  const uint4 wa = ld16(wp), wb = ld16(wp + 64);
+  const uint32_t ww[8] = {wa.x, wa.y, wa.z, wa.w, wb.x, wb.y, wb.z, wb.w};
+  const uint32_t c[4] = {cosv.x, cosv.y, cosv.z, cosv.w}, sn[4] = {sinv.x, sinv.y, sinv.z, sinv.w};
+  uint32_t o1[4], o2[4];
+#pragma unroll
+  for (int e = 0; e < 4; ++e) {                         // x1 = words 0..3, x2 = words 4..7
+    // (x * rsqrt).to(bf16) * weight
+    const uint32_t n1 = mul2(pack_rn(lo_f(xw[e]) * rs, hi_f(xw[e]) * rs), ww[e]);
+    const uint32_t n2 = mul2(pack_rn(lo_f(xw[4 + e]) * rs, hi_f(xw[4 + e]) * rs), ww[4 + e]);
+    o1[e] = sub2(mul2(n1, c[e]), mul2(n2, sn[e]));      // x1*cos - x2*sin, each op rounded
+    o2[e] = add2(mul2(n2, c[e]), mul2(n1, sn[e]));      // x2*cos + x1*sin
+  }
+  Row r;
+  r.a = make_uint4(o1[0], o1[1], o1[2], o1[3]);
+  r.b = make_uint4(o2[0], o2[1], o2[2], o2[3]);
+  return r;
+}
+
+// All heads of one tensor (q, k or v) of one token: 4 heads per pass, kUnroll passes in flight.
+// kNorm: apply RMSNorm + RoPE and store to dst; kCache: also store the row at cache_dst.
+template <bool kNorm, bool kCache>
+__device__ __forceinline__ void token_heads(const __nv_bfloat16* src, __nv_bfloat16* dst, __nv_bfloat16* cache_dst,
+                                            long long cache_head_st, int H, int quarter, const __nv_bfloat16* w,
+                                            const uint4& cosv, const uint4& sinv, float eps, unsigned qmask) {
+#pragma unroll 1
+  for (int h0 = 0; h0 < H; h0 += 4 * kUnroll) {
+    // straight-line body: rows past the last head re-read head H-1 and only their stores are skipped
+    Row x[kUnroll];
+#pragma unroll
+    for (int u = 0; u < kUnroll; ++u) {
+      const int h = min(h0 + 4 * u + quarter, H - 1);
+      x[u].a = ld16_stream(src + h * kD);
+      x[u].b = ld16_stream(src + h * kD + 64);
     }
 #pragma unroll
-    for (int i = 0; i < kUnroll; ++i) {
-      if (un[i].kind < 0) continue;   // uniform per half-warp; shuffles below use the half-warp mask
-      const unsigned hmask = 0xffffu << (threadIdx.x & 16);
-      if (un[i].kind != 2 && p.norm_rope) {
-        float x1[4], x2[4];
-        unpack4(x[i].a, x1);
-        unpack4(x[i].b, x2);
-        float ss = 0.f;
-#pragma unroll
-        for (int e = 0; e < 4; ++e) ss += x1[e] * x1[e];   // squares of bf16 are exact in fp32
-#pragma unroll
-        for (int e = 0; e < 4; ++e) ss += x2[e] * x2[e];
-#pragma unroll
-        for (int o = 8; o >= 1; o >>= 1) ss += __shfl_xor_sync(hmask, ss, o);
-        // torch.rsqrt on the CPU is 1 / sqrt(x), both correctly rounded; so are these
-        const float rs = __frcp_rn(__fsqrt_rn(ss * (1.0f / kD) + p.eps));
-        const __nv_bfloat16* w = (un[i].kind == 0 ? p.q_w : p.k_w) + e0;
-        float w1[4], w2[4], c[4], s[4];
-        unpack4(ld8(w), w1);
-        unpack4(ld8(w + 64), w2);
-        unpack4(cs[i][0], c);
-        unpack4(cs[i][1], s);
-#pragma unroll
-        for (int e = 0; e < 4; ++e) {
-          const float n1 = rbf(rbf(x1[e] * rs) * w1[e]);   // (x * rsqrt).to(bf16) * weight
-          const float n2 = rbf(rbf(x2[e] * rs) * w2[e]);
-          x1[e] = rbf(rbf(n1 * c[e]) - rbf(n2 * s[e]));    // o1 = x1*cos - x2*sin, each op rounded
-          x2[e] = rbf(rbf(n2 * c[e]) + rbf(n1 * s[e]));    // o2 = x2*cos + x1*sin
+    for (int u = 0; u < kUnroll; ++u) {
+      const int h = h0 + 4 * u + quarter;
+      Row y = x[u];
+      if (kNorm) y = norm_rope_row(x[u], w, cosv, sinv, eps, qmask);
+      if (h < H) {
+        if (kNorm) {
+          st16(dst + h * kD, y.a);
+          st16(dst + h * kD + 64, y.b);
         }
-        x[i].a = pack4(x1);
-        x[i].b = pack4(x2);
-        __nv_bfloat16* dst = un[i].kind == 0 ? p.q_out + un[i].t * p.qo_st : p.k_out + un[i].t * p.ko_st;
-        dst += (long long)un[i].h * kD + e0;
-        st8(dst, x[i].a);
-        st8(dst + 64, x[i].b);
-      }
-      if (slot[i] >= 0) {   // padding tokens carry slot -1 (cache_kernels.cu convention)
-        const long long blk = slot[i] / p.block_size;
-        const long long off = slot[i] - blk * p.block_size;
-        __nv_bfloat16* dst = (un[i].kind == 1 ? p.k_cache : p.v_cache) + blk * p.blk_st + off * p.tok_st +
-                             (long long)un[i].h * p.head_st + e0;
-        st8(dst, x[i].a);
-        st8(dst + 64, x[i].b);
+        if (kCache) {
+          st16(cache_dst + h * cache_head_st, y.a);
+          st16(cache_dst + h * cache_head_st + 64, y.b);
+        }
       }
     }
   }
 }
 
-bool aligned8(const void* p) { return (reinterpret_cast<uintptr_t>(p) & 7) == 0; }
+template <int kMinCtas>
+__global__ void __launch_bounds__(kThreads, kMinCtas) prologue_kernel(const PrologueParams p) {
+  const int lane = threadIdx.x & 31;
+  const int quarter = lane >> 3;
+  const int e0 = 8 * (lane & 7);
+  const unsigned qmask = 0xffu << (8 * quarter);
+  const long long warp0 = (long long)blockIdx.x * kWarpsPerCta + (threadIdx.x >> 5);
+  const long long nwarps = (long long)gridDim.x * kWarpsPerCta;
+
+  for (long long t = warp0; t < p.T; t += nwarps) {
+    long long slot = -1;
+    if (p.slots) slot = p.slots[t];
+    __nv_bfloat16 *kc = nullptr, *vc = nullptr;
+    if (slot >= 0) {   // padding tokens carry slot -1 (cache_kernels.cu:292-297)
+      const long long blk = p.bs_shift >= 0 ? (slot >> p.bs_shift) : slot / p.block_size;
+      const long long off = blk * p.blk_st + (slot - blk * p.block_size) * p.tok_st + e0;
+      kc = p.k_cache + off;
+      vc = p.v_cache + off;
+    }
+    if (p.norm_rope) {
+      const __nv_bfloat16* cs = p.cache + p.pos[t] * kD + e0;
+      const uint4 cosv = ld16(cs), sinv = ld16(cs + 64);
+      const __nv_bfloat16* w = p.q_w + e0;
+      token_heads<true, false>(p.q + t * p.q_st + e0, p.q_out + t * p.qo_st + e0, nullptr, 0, p.Hq, quarter, w,
+                               cosv, sinv, p.eps, qmask);
+      w = p.k_w + e0;
+      if (slot >= 0)
+        token_heads<true, true>(p.k + t * p.k_st + e0, p.k_out + t * p.ko_st + e0, kc, p.head_st, p.Hkv, quarter, w,
+                                cosv, sinv, p.eps, qmask);
+      else
+        token_heads<true, false>(p.k + t * p.k_st + e0, p.k_out + t * p.ko_st + e0, nullptr, 0, p.Hkv, quarter, w,
+                                 cosv, sinv, p.eps, qmask);
+    } else if (slot >= 0) {
+      token_heads<false, true>(p.k + t * p.k_st + e0, nullptr, kc, p.head_st, p.Hkv, quarter, nullptr, uint4{}, uint4{},
+                               0.f, qmask);
+    }
+    if (slot >= 0)
+      token_heads<false, true>(p.v + t * p.v_st + e0, nullptr, vc, p.head_st, p.Hkv, quarter, nullptr, uint4{}, uint4{},
+                               0.f, qmask);
+  }
+}
+
+bool aligned16(const void* p) { return (reinterpret_cast<uintptr_t>(p) & 15) == 0; }
 
 int launch(const PrologueParams& p, cudaStream_t s) {
   reset_launch_count();
-  if (p.units == 0) return TMX_OK;
+  if (p.T == 0) return TMX_OK;
   int st = check_arch();
   if (st != TMX_OK) return st;
-  const long long per_cta = (long long)kHalfWarpsPerCta * kUnroll;
-  long long want = (p.units + per_cta - 1) / per_cta;
-  const long long cap = (long long)device_sm_count() * 8 * 4;   // 8 resident CTAs/SM x 4 waves
-  unsigned grid = (unsigned)(want < cap ? want : cap);
-  prologue_kernel<<<grid, kThreads, 0, s>>>(p);
+  static int ctas_per_sm = 0;
+  static void (*kernel)(const PrologueParams) = nullptr;
+  if (ctas_per_sm == 0) {
+    const char* e = std::getenv("TMX_PROLOGUE_VARIANT");   // developer switch: 1 = 4 CTAs/SM build (64 regs, small spill)
+    kernel = (e && std::atoi(e) == 1) ? prologue_kernel<4> : prologue_kernel<kMinCtasPerSm>;
+    TMX_CUDA_TRY(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&ctas_per_sm, kernel, kThreads, 0));
+    if (ctas_per_sm <= 0) ctas_per_sm = 1;
+  }
+  PrologueParams pp = p;
+  pp.bs_shift = -1;
+  for (int b = 0; b < 31; ++b)
+    if (p.block_size == (1 << b)) pp.bs_shift = b;
+  const long long want = ((long long)p.T + kWarpsPerCta - 1) / kWarpsPerCta;
+  const long long cap = (long long)device_sm_count() * ctas_per_sm * 2;   // 2 waves of resident CTAs
+  const unsigned grid = (unsigned)(want < cap ? want : cap);
+  kernel<<<grid, kThreads, 0, s>>>(pp);
   count_launch();
   TMX_CUDA_TRY(cudaGetLastError());
   return TMX_OK;
@@ -210,10 +256,10 @@ extern "C" int tmx_qk_norm_rope(void* q_out, void* k_out, const void* q, const v
                              cache ? v_stride_t : 0, cache ? cache_block_stride : 0,
                              cache ? cache_token_stride : 0, cache ? cache_head_stride : 0};
   for (int64_t sdt : strides)
-    if (sdt % 4 != 0) return TMX_ERR_ALIGNMENT;
+    if (sdt % 8 != 0) return TMX_ERR_ALIGNMENT;
   const void* ptrs[] = {q_out, k_out, q, k, q_weight, k_weight, cos_sin_cache, v, k_cache, v_cache};
   for (const void* ptr : ptrs)
-    if (!aligned8(ptr)) return TMX_ERR_ALIGNMENT;
+    if (!aligned16(ptr)) return TMX_ERR_ALIGNMENT;
   PrologueParams p{};
   p.q = (const __nv_bfloat16*)q; p.k = (const __nv_bfloat16*)k; p.v = (const __nv_bfloat16*)v;
   p.q_out = (__nv_bfloat16*)q_out; p.k_out = (__nv_bfloat16*)k_out;
@@ -223,8 +269,7 @@ extern "C" int tmx_qk_norm_rope(void* q_out, void* k_out, const void* q, const v
   p.slots = cache ? (const long long*)slot_mapping : nullptr;
   p.q_st = q_stride_t; p.k_st = k_stride_t; p.v_st = v_stride_t; p.qo_st = qo_stride_t; p.ko_st = ko_stride_t;
   p.blk_st = cache_block_stride; p.tok_st = cache_token_stride; p.head_st = cache_head_stride;
-  p.T = T; p.Hq = Hq; p.Hkv = Hkv; p.upt = Hq + Hkv + (cache ? Hkv : 0);
-  p.units = (long long)T * p.upt;
+  p.T = T; p.Hq = Hq; p.Hkv = Hkv;
   p.block_size = block_size; p.max_pos = max_pos; p.norm_rope = 1; p.eps = eps;
   return launch(p, (cudaStream_t)stream);
 }
@@ -241,16 +286,15 @@ extern "C" int tmx_reshape_and_cache_flash(const void* key, const void* value, v
   if (k_stride_t < (int64_t)Hkv * D || v_stride_t < (int64_t)Hkv * D || cache_head_stride < D) return TMX_ERR_BAD_SHAPE;
   const int64_t strides[] = {k_stride_t, v_stride_t, cache_block_stride, cache_token_stride, cache_head_stride};
   for (int64_t sdt : strides)
-    if (sdt % 4 != 0) return TMX_ERR_ALIGNMENT;
-  if (!aligned8(key) || !aligned8(value) || !aligned8(k_cache) || !aligned8(v_cache)) return TMX_ERR_ALIGNMENT;
+    if (sdt % 8 != 0) return TMX_ERR_ALIGNMENT;
+  if (!aligned16(key) || !aligned16(value) || !aligned16(k_cache) || !aligned16(v_cache)) return TMX_ERR_ALIGNMENT;
   PrologueParams p{};
   p.k = (const __nv_bfloat16*)key; p.v = (const __nv_bfloat16*)value;
   p.k_cache = (__nv_bfloat16*)k_cache; p.v_cache = (__nv_bfloat16*)v_cache;
   p.slots = (const long long*)slot_mapping;
   p.k_st = k_stride_t; p.v_st = v_stride_t;
   p.blk_st = cache_block_stride; p.tok_st = cache_token_stride; p.head_st = cache_head_stride;
-  p.T = T; p.Hq = 0; p.Hkv = Hkv; p.upt = 2 * Hkv;
-  p.units = (long long)T * p.upt;
+  p.T = T; p.Hq = 0; p.Hkv = Hkv;
   p.block_size = block_size; p.norm_rope = 0;
   return launch(p, (cudaStream_t)stream);
 }
