@@ -211,27 +211,38 @@ def main():
     q = q_host.to(dev).view(n, hq * D)
     k = k_host.to(dev).view(n, hkv * D)
     v = v_host.to(dev).view(n, hkv * D)
-    out = torch.empty((n, hq * D), dtype=torch.bfloat16, device=dev)
-    gathered = torch.empty((world, n, hq * D), dtype=torch.bfloat16, device=dev) if world > 1 else None
+    # two output / gather buffers: the all-gather of layer L runs on NCCL's stream while layer L+1
+    # computes into the other buffer ("overlap with the next layer's attention")
+    outs = [torch.empty((n, hq * D), dtype=torch.bfloat16, device=dev) for _ in range(2 if world > 1 else 1)]
+    out = outs[0]
+    gathered = [torch.empty((world, n, hq * D), dtype=torch.bfloat16, device=dev) for _ in range(2)] \
+        if world > 1 else None
 
     cfg = tmx.TriangleMixConfig(SI, SL, LAST, triangle_layer_indices=list(TRIANGLE_LAYERS))
     scale = D ** -0.5
     layers = [tmx.TriangleMixImpl(hq, D, scale, num_kv_heads=hkv, trianglemix_config=cfg, layer_idx=i,
                                   num_layers=NUM_LAYERS, kernel=args.kernel) for i in range(NUM_LAYERS)]
     meta = tmx.TriangleMixMetadataBuilder.from_seq_lens([n], dev)
-    side = torch.cuda.Stream(device=dev) if world > 1 else None
     launches = [0]
 
     def step(qd, kd, vd, events=None):
+        pending = [None, None]
         for i, impl in enumerate(layers):
+            b = i % len(outs)
+            if pending[b] is not None:      # this buffer's previous gather must be done before it is overwritten
+                pending[b].wait()
+                pending[b] = None
             if events is not None:
                 events[i][0].record()
-            impl.forward(None, qd, kd, vd, None, meta, output=out)
+            impl.forward(None, qd, kd, vd, None, meta, output=outs[b])
             launches[0] += ops.last_launch_count()
             if events is not None:
                 events[i][1].record()
-            if world > 1:          # output all-gather of this layer's [T, Hq/P, D] shard
-                dist.all_gather_into_tensor(gathered.view(-1), out.view(-1))
+            if world > 1:          # output all-gather of this layer's [T, Hq/P, D] shard, asynchronous
+                pending[b] = dist.all_gather_into_tensor(gathered[b].view(-1), outs[b].view(-1), async_op=True)
+        for w in pending:
+            if w is not None:
+                w.wait()
 
     def barrier():
         torch.cuda.synchronize()
@@ -273,7 +284,7 @@ def main():
         kd = k_host.to(dev, non_blocking=True).view(n, hkv * D)
         vd = v_host.to(dev, non_blocking=True).view(n, hkv * D)
         step(qd, kd, vd)
-        out_host.copy_(out, non_blocking=True)
+        out_host.copy_(outs[(NUM_LAYERS - 1) % len(outs)], non_blocking=True)
     e2e_step()
     barrier()
     t0.record()
@@ -286,8 +297,42 @@ def main():
         dist.all_reduce(ms2, op=dist.ReduceOp.MAX)
     e2e_ms = float(ms2.item()) / args.steps
 
+    # ---- the step in front of attention, reported beside the metric --------
+    # fused q/k RMSNorm + RoPE + KV-cache write, in place on a packed [T, (Hq+2Hkv)*D] qkv buffer of
+    # this rank's heads; 1.6 GB/P of inputs, larger than L2 at every P the bench runs.
+    prologue = None
+    if rank == 0:
+        qkv = torch.randn(n, (hq + 2 * hkv) * D, device=dev, dtype=torch.bfloat16)
+        pq, pk, pv = qkv.split([hq * D, hkv * D, hkv * D], dim=-1)
+        w1 = torch.ones(D, device=dev, dtype=torch.bfloat16)
+        cs_cache = tmx.compute_cos_sin_cache(D, n, 1000000.0, device=dev)
+        pos = torch.arange(n, device=dev)
+        bs = 16
+        kvc = torch.zeros(2, (n + bs - 1) // bs, bs, hkv, D, device=dev, dtype=torch.bfloat16)
+        slots = torch.arange(n, device=dev)
+
+        def pro():
+            ops.qk_norm_rope(pos, pq, pk, w1, w1, cs_cache, 1e-6, D, inplace=True, v=pv, key_cache=kvc[0],
+                             value_cache=kvc[1], slot_mapping=slots)
+        for _ in range(3):
+            pro()
+        torch.cuda.synchronize()
+        t0.record()
+        for _ in range(10):
+            pro()
+        t1.record()
+        torch.cuda.synchronize()
+        pms = t0.elapsed_time(t1) / 10
+        pbytes = 2 * n * (hq + hkv) * D * 2 + 3 * n * hkv * D * 2 + n * D * 2 + 2 * n * 8
+        prologue = {"kernel": "fused q/k RMSNorm + NeoX RoPE + KV-cache write (tmx_qk_norm_rope)", "ms": pms,
+                    "algorithmic_bytes": pbytes, "achieved": pbytes / pms / 1e6, "unit": "GB/s", "bound": "hbm"}
+        del qkv, kvc
+
     if rank == 0:
         peaks = load_peaks()
+        if prologue is not None and peaks.get("hbm_gbs"):
+            prologue["peak"] = peaks["hbm_gbs"]
+            prologue["frac"] = prologue["achieved"] / peaks["hbm_gbs"]
         pairs_dense = n * (n + 1) // 2
         flops_dense = 4.0 * D * hq * pairs_dense
         achieved = flops_dense / (dense_avg * 1e-3) / 1e12
@@ -306,6 +351,7 @@ def main():
                         "h2d_bytes_per_step": (q_host.numel() + k_host.numel() + v_host.numel()) * 2,
                         "d2h_bytes_per_step": out_host.numel() * 2, "ms_per_step": e2e_ms},
                 "gpu_launches": n_launch,
+                "prologue": prologue,
                 "roofline": {"bound": "tensor", "kernel": "dense-causal attention layer (per rank)",
                              "achieved": achieved, "peak": peaks["tflops"], "unit": "TFLOP/s",
                              "frac": achieved / peaks["tflops"], "traffic": traffic,
