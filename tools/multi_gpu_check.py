@@ -1,0 +1,106 @@
+"""Multi-GPU parity of the head-sharded path on real GPUs (NCCL): every rank computes its head
+shard with the CUDA kernels, the shards are all-gathered, and rank 0 compares the gathered tensor
+with the same layer computed on ONE GPU with all heads.  Heads never interact, so dense layers
+must be bit-identical.  In triangle layers the dense-tail rows are split over the keys into as many
+chunks as fill the SMs (tmx_api.cu: sm_count / (B * Hkv)), so the per-rank head count changes the fp32
+merge order of those last-1 rows: they must agree within the attention tolerance (atol 1.5e-2 /
+rtol 1e-2) and every other row must still be bit-identical.  BASELINE configs[3] (Qwen3-32B heads, one 128K... here a
+shorter prompt by default) and configs[4] (8 ragged sequences).
+
+    python -m torch.distributed.run --nnodes=1 --nproc-per-node P --master-addr 127.0.0.1 \
+        --master-port 29511 tools/multi_gpu_check.py [--n 32768]
+"""
+import argparse
+import json
+import os
+import sys
+sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
+import torch
+import torch.distributed as dist
+import vllm_trianglemix_b200 as tmx
+from vllm_trianglemix_b200 import head_shard
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--n", type=int, default=32768)
+    ap.add_argument("--out", default=None)
+    args = ap.parse_args()
+    rank, world, local = (int(os.environ[k]) for k in ("RANK", "WORLD_SIZE", "LOCAL_RANK"))
+    dev = torch.device("cuda", local)
+    torch.cuda.set_device(dev)
+    dist.init_process_group("nccl", device_id=dev)
+    d, si, sl, last = 128, 4, 32, 64
+    results = []
+    cases = [("config4_qwen3_32b_heads", 64, 8, [args.n]),
+             ("config5_varlen_8seq", 32, 8, [8192, 12288, 16384, 24576, 32768, 40960, 49152, 65536])]
+    for name, hq_tot, hkv_tot, seq_lens in cases:
+        if name.startswith("config5") and args.n < 32768:
+            seq_lens = [x // 8 for x in seq_lens]
+        t = sum(seq_lens)
+        part = head_shard.head_partition(rank, world, hq_tot, hkv_tot)
+        g = torch.Generator().manual_seed(1234)
+        q = torch.randn(t, hq_tot, d, generator=g).bfloat16()
+        k = torch.randn(t, hkv_tot, d, generator=g).bfloat16()
+        v = torch.randn(t, hkv_tot, d, generator=g).bfloat16()
+        cfg = tmx.TriangleMixConfig(si, sl, last, triangle_layer_indices=[1])
+        meta = tmx.TriangleMixMetadataBuilder.from_seq_lens(seq_lens, dev)
+        for layer_idx in (0, 1):
+            impl = tmx.TriangleMixImpl(part.num_heads, d, d ** -0.5, num_kv_heads=part.num_kv_heads,
+                                       trianglemix_config=cfg, layer_idx=layer_idx, num_layers=2)
+            qs = head_shard.shard_heads(q, part, "q").contiguous().to(dev)
+            ks = head_shard.shard_heads(k, part, "kv").contiguous().to(dev)
+            vs = head_shard.shard_heads(v, part, "kv").contiguous().to(dev)
+            out = torch.empty(t, part.num_heads * d, dtype=torch.bfloat16, device=dev)
+            impl.forward(None, qs.view(t, -1), ks.view(t, -1), vs.view(t, -1), None, meta, output=out)
+            e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            torch.cuda.synchronize()
+            dist.barrier()
+            e0.record()
+            gathered, _ = head_shard.all_gather_heads(out.view(t, part.num_heads, d))
+            e1.record()
+            torch.cuda.synchronize()
+            gather_ms = e0.elapsed_time(e1)
+            full = head_shard.heads_from_gathered(gathered)
+            if rank == 0:
+                one = tmx.TriangleMixImpl(hq_tot, d, d ** -0.5, num_kv_heads=hkv_tot, trianglemix_config=cfg,
+                                          layer_idx=layer_idx, num_layers=2)
+                ref = torch.empty(t, hq_tot * d, dtype=torch.bfloat16, device=dev)
+                one.forward(None, q.to(dev).view(t, -1), k.to(dev).view(t, -1), v.to(dev).view(t, -1), None, meta,
+                            output=ref)
+                torch.cuda.synchronize()
+                got = full.reshape(t, -1)
+                same = torch.equal(got, ref)
+                diff = (got.float() - ref.float()).abs()
+                viol = int((diff > 1.5e-2 + 1e-2 * ref.float().abs()).sum().item())
+                rows_diff = (got != ref).any(dim=1)
+                # rows outside the dense tail of their sequence must not differ at all
+                tail = torch.zeros(t, dtype=torch.bool, device=dev)
+                s0 = 0
+                for ln in seq_lens:
+                    tail[s0 + max(0, ln - last + 1):s0 + ln] = True
+                    s0 += ln
+                stray = int((rows_diff & ~tail).sum().item())
+                ok = same if layer_idx == 0 else (viol == 0 and stray == 0)
+                results.append({"case": name, "layer": "triangle" if layer_idx == 1 else "dense", "world": world,
+                                "tokens": t, "heads_per_rank": [part.num_heads, part.num_kv_heads],
+                                "ok": bool(ok), "bit_identical_to_1gpu": bool(same),
+                                "max_abs_diff": float(diff.max().item()), "tolerance_violations": viol,
+                                "rows_differing": int(rows_diff.sum().item()),
+                                "rows_differing_outside_dense_tail": stray, "all_gather_ms": gather_ms,
+                                "all_gather_GBps_per_rank": out.numel() * 2 * (world - 1) / gather_ms / 1e6})
+                print(json.dumps(results[-1]), flush=True)
+                del ref
+            del gathered, full, out
+    if rank == 0:
+        ok = all(r["ok"] for r in results)
+        if args.out:
+            with open(args.out, "w") as f:
+                json.dump(results, f, indent=1)
+        print("multi_gpu_check", "OK" if ok else "MISMATCH", flush=True)
+    dist.barrier()
+    dist.destroy_process_group()
+
+
+if __name__ == "__main__":
+    main()
