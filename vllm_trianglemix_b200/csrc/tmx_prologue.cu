@@ -122,42 +122,13 @@ __device__ __forceinline__ Row norm_rope_row(const Row& x, const __nv_bfloat16* 
   return r;
 }
 
-// All heads of one tensor (q, k or v) of one token: 4 heads per pass, kUnroll passes in flight.
-// kNorm: apply RMSNorm + RoPE and store to dst; kCache: also store the row at cache_dst.
-template <bool kNorm, bool kCache>
-__device__ __forceinline__ void token_heads(const __nv_bfloat16* src, __nv_bfloat16* dst, __nv_bfloat16* cache_dst,
-                                            long long cache_head_st, int H, int quarter, const __nv_bfloat16* w,
-                                            const uint4& cosv, const uint4& sinv, float eps, unsigned qmask) {
-#pragma unroll 1
-  for (int h0 = 0; h0 < H; h0 += 4 * kUnroll) {
-    // straight-line body: rows past the last head re-read head H-1 and only their stores are skipped
-    Row x[kUnroll];
-#pragma unroll
-    for (int u = 0; u < kUnroll; ++u) {
-      const int h = min(h0 + 4 * u + quarter, H - 1);
-      x[u].a = ld16_stream(src + h * kD);
-      x[u].b = ld16_stream(src + h * kD + 64);
-    }
-#pragma unroll
-    for (int u = 0; u < kUnroll; ++u) {
-      const int h = h0 + 4 * u + quarter;
-      Row y = x[u];
-      if (kNorm) y = norm_rope_row(x[u], w, cosv, sinv, eps, qmask);
-      if (h < H) {
-        if (kNorm) {
-          st16(dst + h * kD, y.a);
-          st16(dst + h * kD + 64, y.b);
-        }
-        if (kCache) {
-          st16(cache_dst + h * cache_head_st, y.a);
-          st16(cache_dst + h * cache_head_st + 64, y.b);
-        }
-      }
-    }
-  }
-}
-
-template <int kMinCtas>
+// One token per warp iteration.  The token's head rows form one list -- q heads, k heads, then
+// (when the cache is written) v heads -- walked 4 rows per pass (one per quarter-warp), kUnroll
+// passes in flight, so a rank that holds 4 + 1 + 1 rows per token (Qwen3-8B over 8 GPUs) issues
+// them in one round trip.  The body is straight-line: rows past the end re-read the last row and
+// only their stores are predicated off; v rows run through the norm arithmetic and keep the raw
+// value (a select) instead of branching around it.
+template <bool kNorm, int kMinCtas>
 __global__ void __launch_bounds__(kThreads, kMinCtas) prologue_kernel(const PrologueParams p) {
   const int lane = threadIdx.x & 31;
   const int quarter = lane >> 3;
@@ -165,37 +136,61 @@ __global__ void __launch_bounds__(kThreads, kMinCtas) prologue_kernel(const Prol
   const unsigned qmask = 0xffu << (8 * quarter);
   const long long warp0 = (long long)blockIdx.x * kWarpsPerCta + (threadIdx.x >> 5);
   const long long nwarps = (long long)gridDim.x * kWarpsPerCta;
+  const int hqk = p.Hq + p.Hkv;
+  const int rows = hqk + (p.slots ? p.Hkv : 0);
 
   for (long long t = warp0; t < p.T; t += nwarps) {
     long long slot = -1;
     if (p.slots) slot = p.slots[t];
-    __nv_bfloat16 *kc = nullptr, *vc = nullptr;
+    long long coff = 0;
     if (slot >= 0) {   // padding tokens carry slot -1 (cache_kernels.cu:292-297)
       const long long blk = p.bs_shift >= 0 ? (slot >> p.bs_shift) : slot / p.block_size;
-      const long long off = blk * p.blk_st + (slot - blk * p.block_size) * p.tok_st + e0;
-      kc = p.k_cache + off;
-      vc = p.v_cache + off;
+      coff = blk * p.blk_st + (slot - blk * p.block_size) * p.tok_st + e0;
     }
-    if (p.norm_rope) {
+    uint4 cosv = uint4{}, sinv = uint4{};
+    if (kNorm) {
       const __nv_bfloat16* cs = p.cache + p.pos[t] * kD + e0;
-      const uint4 cosv = ld16(cs), sinv = ld16(cs + 64);
-      const __nv_bfloat16* w = p.q_w + e0;
-      token_heads<true, false>(p.q + t * p.q_st + e0, p.q_out + t * p.qo_st + e0, nullptr, 0, p.Hq, quarter, w,
-                               cosv, sinv, p.eps, qmask);
-      w = p.k_w + e0;
-      if (slot >= 0)
-        token_heads<true, true>(p.k + t * p.k_st + e0, p.k_out + t * p.ko_st + e0, kc, p.head_st, p.Hkv, quarter, w,
-                                cosv, sinv, p.eps, qmask);
-      else
-        token_heads<true, false>(p.k + t * p.k_st + e0, p.k_out + t * p.ko_st + e0, nullptr, 0, p.Hkv, quarter, w,
-                                 cosv, sinv, p.eps, qmask);
-    } else if (slot >= 0) {
-      token_heads<false, true>(p.k + t * p.k_st + e0, nullptr, kc, p.head_st, p.Hkv, quarter, nullptr, uint4{}, uint4{},
-                               0.f, qmask);
+      cosv = ld16(cs);
+      sinv = ld16(cs + 64);
     }
-    if (slot >= 0)
-      token_heads<false, true>(p.v + t * p.v_st + e0, nullptr, vc, p.head_st, p.Hkv, quarter, nullptr, uint4{}, uint4{},
-                               0.f, qmask);
+    const __nv_bfloat16* qrow = p.q + t * p.q_st + e0;
+    const __nv_bfloat16* krow = p.k + t * p.k_st + e0 - (long long)p.Hq * kD;          // indexed by list row j
+    const __nv_bfloat16* vrow = p.v + t * p.v_st + e0 - (long long)hqk * kD;
+    __nv_bfloat16* qdst = p.q_out + t * p.qo_st + e0;
+    __nv_bfloat16* kdst = p.k_out + t * p.ko_st + e0 - (long long)p.Hq * kD;
+
+#pragma unroll 1
+    for (int j0 = 0; j0 < rows; j0 += 4 * kUnroll) {
+      Row x[kUnroll];
+#pragma unroll
+      for (int u = 0; u < kUnroll; ++u) {
+        const int j = min(j0 + 4 * u + quarter, rows - 1);
+        const __nv_bfloat16* src = (j < p.Hq ? qrow : j < hqk ? krow : vrow) + j * kD;
+        x[u].a = ld16_stream(src);
+        x[u].b = ld16_stream(src + 64);
+      }
+#pragma unroll
+      for (int u = 0; u < kUnroll; ++u) {
+        const int j = j0 + 4 * u + quarter;
+        const bool is_q = j < p.Hq, is_v = j >= hqk;
+        Row y = x[u];
+        if (kNorm) {
+          const Row n = norm_rope_row(x[u], (is_q ? p.q_w : p.k_w) + e0, cosv, sinv, p.eps, qmask);
+          if (!is_v) y = n;
+          if (j < hqk) {
+            __nv_bfloat16* dst = (is_q ? qdst : kdst) + j * kD;
+            st16(dst, y.a);
+            st16(dst + 64, y.b);
+          }
+        }
+        if (slot >= 0 && !is_q && j < rows) {
+          __nv_bfloat16* dst = (is_v ? p.v_cache + (long long)(j - hqk) * p.head_st
+                                     : p.k_cache + (long long)(j - p.Hq) * p.head_st) + coff;
+          st16(dst, y.a);
+          st16(dst + 64, y.b);
+        }
+      }
+    }
   }
 }
 
@@ -208,9 +203,12 @@ int launch(const PrologueParams& p, cudaStream_t s) {
   if (st != TMX_OK) return st;
   static int ctas_per_sm = 0;
   static void (*kernel)(const PrologueParams) = nullptr;
+  static void (*copy_kernel)(const PrologueParams) = nullptr;
   if (ctas_per_sm == 0) {
     const char* e = std::getenv("TMX_PROLOGUE_VARIANT");   // developer switch: 1 = 4 CTAs/SM build (64 regs, small spill)
-    kernel = (e && std::atoi(e) == 1) ? prologue_kernel<4> : prologue_kernel<kMinCtasPerSm>;
+    const bool v1 = e && std::atoi(e) == 1;
+    kernel = v1 ? prologue_kernel<true, 4> : prologue_kernel<true, kMinCtasPerSm>;
+    copy_kernel = prologue_kernel<false, kMinCtasPerSm>;
     TMX_CUDA_TRY(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&ctas_per_sm, kernel, kThreads, 0));
     if (ctas_per_sm <= 0) ctas_per_sm = 1;
   }
@@ -221,7 +219,7 @@ int launch(const PrologueParams& p, cudaStream_t s) {
   const long long want = ((long long)p.T + kWarpsPerCta - 1) / kWarpsPerCta;
   const long long cap = (long long)device_sm_count() * ctas_per_sm * 2;   // 2 waves of resident CTAs
   const unsigned grid = (unsigned)(want < cap ? want : cap);
-  kernel<<<grid, kThreads, 0, s>>>(pp);
+  (p.norm_rope ? kernel : copy_kernel)<<<grid, kThreads, 0, s>>>(pp);
   count_launch();
   TMX_CUDA_TRY(cudaGetLastError());
   return TMX_OK;
