@@ -217,10 +217,9 @@ def main():
     v = v_host.to(dev).view(n, hkv * D)
     # two output / gather buffers: the all-gather of layer L runs on NCCL's stream while layer L+1
     # computes into the other buffer ("overlap with the next layer's attention")
-    outs = [torch.empty((n, hq * D), dtype=torch.bfloat16, device=dev) for _ in range(2 if world > 1 else 1)]
-    out = outs[0]
-    gathered = [torch.empty((world, n, hq * D), dtype=torch.bfloat16, device=dev) for _ in range(2)] \
-        if world > 1 else None
+    from vllm_trianglemix_b200 import head_shard
+    og = head_shard.OverlappedGather((n, hq * D), torch.bfloat16, dev, depth=2) if world > 1 else None
+    out = torch.empty((n, hq * D), dtype=torch.bfloat16, device=dev) if world == 1 else None
 
     cfg = tmx.TriangleMixConfig(SI, SL, LAST, triangle_layer_indices=list(TRIANGLE_LAYERS))
     scale = D ** -0.5
@@ -230,23 +229,19 @@ def main():
     launches = [0]
 
     def step(qd, kd, vd, events=None):
-        pending = [None, None]
         for i, impl in enumerate(layers):
-            b = i % len(outs)
-            if pending[b] is not None:      # this buffer's previous gather must be done before it is overwritten
-                pending[b].wait()
-                pending[b] = None
+            o = out if og is None else og.buffer(i)
             if events is not None:
                 events[i][0].record()
-            impl.forward(None, qd, kd, vd, None, meta, output=outs[b])
+            impl.forward(None, qd, kd, vd, None, meta, output=o)
             launches[0] += ops.last_launch_count()
             if events is not None:
                 events[i][1].record()
-            if world > 1:          # output all-gather of this layer's [T, Hq/P, D] shard, asynchronous
-                pending[b] = dist.all_gather_into_tensor(gathered[b].view(-1), outs[b].view(-1), async_op=True)
-        for w in pending:
-            if w is not None:
-                w.wait()
+            if og is not None:     # output all-gather of this layer's [T, Hq/P, D] shard, asynchronous
+                og.launch(i)
+        if og is not None:
+            og.finish()
+        return o
 
     def barrier():
         torch.cuda.synchronize()
@@ -287,8 +282,7 @@ def main():
         qd = q_host.to(dev, non_blocking=True).view(n, hq * D)
         kd = k_host.to(dev, non_blocking=True).view(n, hkv * D)
         vd = v_host.to(dev, non_blocking=True).view(n, hkv * D)
-        step(qd, kd, vd)
-        out_host.copy_(outs[(NUM_LAYERS - 1) % len(outs)], non_blocking=True)
+        out_host.copy_(step(qd, kd, vd), non_blocking=True)
     e2e_step()
     barrier()
     t0.record()

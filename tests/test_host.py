@@ -178,6 +178,42 @@ def test_backend_forward_contract_without_gpu():
     assert modes[0][0] == ops.DENSE_CAUSAL and modes[1] == (ops.TRIANGLE, 4, 32, 64)
 
 
+# ------------------------------------------------------------------ the step in front of attention
+def test_qwen3_block_heads_per_rank_and_no_cpu_path():
+    """Heads per tensor-parallel rank as reference qwen3.py:85-98; CPU tensors are refused."""
+    for tp, want in ((1, (32, 8)), (2, (16, 4)), (8, (4, 1)), (16, (2, 1))):
+        blk = tmx.Qwen3TriangleMixAttention(32, 8, 128, max_position=64, tp_size=tp)
+        assert (blk.num_heads, blk.num_kv_heads) == want
+        assert blk.q_size == want[0] * 128 and blk.kv_size == want[1] * 128 and blk.scaling == 128 ** -0.5
+    with pytest.raises(AssertionError):
+        tmx.Qwen3TriangleMixAttention(32, 8, tp_size=3)
+    blk = tmx.Qwen3TriangleMixAttention(4, 2, 128, max_position=64, rope_theta=10000.0)
+    assert blk.cos_sin_cache.shape == (64, 128) and blk.cos_sin_cache.dtype == torch.bfloat16
+    assert torch.equal(blk.cos_sin_cache[0, :64], torch.ones(64, dtype=torch.bfloat16))      # cos(0) | sin(0)
+    assert not blk.cos_sin_cache[0, 64:].any()
+    qkv = torch.zeros(3, (4 + 2 * 2) * 128, dtype=torch.bfloat16)
+    meta = tmx.TriangleMixMetadataBuilder.from_seq_lens([3], "cpu")
+    with pytest.raises(_lib.TmxError):
+        blk(torch.arange(3), qkv, None, meta)
+
+
+def test_cache_write_signature_matches_reference_op():
+    """ops.reshape_and_cache_flash keeps the reference's argument list (vllm/_custom_ops.py:1605-1614)."""
+    names = list(inspect.signature(ops.reshape_and_cache_flash).parameters)
+    assert names == ["key", "value", "key_cache", "value_cache", "slot_mapping", "kv_cache_dtype", "k_scale",
+                     "v_scale"]
+    k = torch.zeros(2, 1, 128, dtype=torch.bfloat16)
+    kc = torch.zeros(1, 16, 1, 128, dtype=torch.bfloat16)
+    with pytest.raises(_lib.TmxError):          # CPU tensors: no fallback
+        ops.reshape_and_cache_flash(k, k, kc, kc, torch.zeros(2, dtype=torch.int64), "auto", None, None)
+    # metadata carries slot_mapping through the builder (flash_attn.py:127)
+    import types
+    m = types.SimpleNamespace(num_actual_tokens=2, max_query_len=2, query_start_loc=torch.tensor([0, 2]),
+                              max_seq_len=2, seq_lens=None, causal=True, slot_mapping=torch.tensor([5, 6]))
+    md = tmx.TriangleMixMetadataBuilder().build(common_attn_metadata=m)
+    assert md.slot_mapping.tolist() == [5, 6]
+
+
 # ------------------------------------------------------------------ head partition
 @pytest.mark.parametrize("hq,hkv", [(32, 8), (64, 8), (16, 8)])
 @pytest.mark.parametrize("world", [1, 2, 4, 8])
@@ -236,6 +272,17 @@ def _gloo_worker(rank, world, port, ret):
         ref = torch.as_tensor(np.asarray(
             orc.attention_varlen_fp32(q, k, v, cu, scale, si, sl, last, orc.TRIANGLE))).to(torch.bfloat16)
         ok = torch.equal(full, ref) and gathered.shape == (world, t, hq // world, d)
+        # the double-buffered asynchronous gather bench.py uses: 5 "layers", each result must be that layer's
+        og = head_shard.OverlappedGather((4, 3), torch.float32, "cpu", depth=2)
+        for i in range(5):
+            og.buffer(i).fill_(100.0 * i + rank)
+            og.launch(i)
+            if i >= 1:          # layer i-1's gather is complete and intact while layer i's is in flight
+                prev = og.result(i - 1)
+                ok = ok and all(bool((prev[r] == 100.0 * (i - 1) + r).all()) for r in range(world))
+        og.finish()
+        ok = ok and all(w is None for w in og.pending)
+        ok = ok and all(bool((og.result(4)[r] == 400.0 + r).all()) for r in range(world))
         # max-over-ranks timing reduction used by bench.py
         ms = torch.tensor([10.0 + rank])
         dist.all_reduce(ms, op=dist.ReduceOp.MAX)

@@ -87,3 +87,48 @@ def heads_from_gathered(gathered: torch.Tensor) -> torch.Tensor:
     """[P, T, Hq/P, D] -> the global [T, Hq, D] view order (a permuted view, no copy)."""
     p, t, h, d = gathered.shape
     return gathered.permute(1, 0, 2, 3).reshape(t, p * h, d)
+
+
+class OverlappedGather:
+    """Per-layer output all-gather that runs behind the next layer's attention.
+
+    Holds ``depth`` (output shard, gathered) buffer pairs.  ``buffer(i)`` hands layer i its output
+    buffer, first waiting for the gather that last used it; ``launch(i)`` starts the asynchronous
+    all-gather of that buffer (``async_op=True``: on NCCL it runs on the communicator's stream while
+    the caller's stream goes on with layer i+1); ``finish()`` waits for everything in flight.  With
+    depth 2 the only exposed gather is the last layer's (and whatever is longer than a layer).
+    """
+
+    def __init__(self, shard_shape, dtype, device, depth: int = 2, group=None):
+        self.group = group
+        self.world = dist.get_world_size(group)
+        self.outs = [torch.empty(shard_shape, dtype=dtype, device=device) for _ in range(depth)]
+        self.gathered = [torch.empty((self.world,) + tuple(shard_shape), dtype=dtype, device=device)
+                         for _ in range(depth)]
+        self.pending = [None] * depth
+
+    def buffer(self, i: int) -> torch.Tensor:
+        b = i % len(self.outs)
+        if self.pending[b] is not None:       # the previous gather out of this buffer must be done
+            self.pending[b].wait()
+            self.pending[b] = None
+        return self.outs[b]
+
+    def launch(self, i: int) -> None:
+        b = i % len(self.outs)
+        self.pending[b] = dist.all_gather_into_tensor(self.gathered[b].view(-1), self.outs[b].view(-1),
+                                                      group=self.group, async_op=True)
+
+    def result(self, i: int) -> torch.Tensor:
+        """The gathered [P, ...] tensor of layer i (waits for its gather)."""
+        b = i % len(self.outs)
+        if self.pending[b] is not None:
+            self.pending[b].wait()
+            self.pending[b] = None
+        return self.gathered[b]
+
+    def finish(self) -> None:
+        for b, w in enumerate(self.pending):
+            if w is not None:
+                w.wait()
+                self.pending[b] = None
