@@ -272,3 +272,42 @@ def test_attention_peaky_softmax(ops, kernel):
         out = ops.prefill_attn(q.to(DEV), k.to(DEV), v.to(DEV), cu, n, 128 ** -0.5, 4, 32, 64, mode, kernel=kernel)
         ref = orc.attention_varlen_fp32(q, k, v, [0, n], 128 ** -0.5, 4, 32, 64, mode)
         _check(out.cpu(), ref, ("peaky", mode, kernel))
+
+
+# ------------------------------------------------------------------ seeded fuzz over the whole parameter space
+def _fuzz_case(seed):
+    import random
+    r = random.Random(seed)
+    b = r.choice([1, 1, 2, 3, 5])
+    lens = []
+    for _ in range(b):
+        kind = r.random()
+        if kind < 0.15:
+            lens.append(r.choice([1, 2, 31, 32, 33, 127, 128, 129, 255, 256, 257, 512]))
+        elif kind < 0.3:
+            lens.append(128 * r.randint(1, 10))
+        else:
+            lens.append(r.randint(1, 1400))
+    hq, hkv = r.choice([(2, 1), (2, 2), (4, 2), (4, 1), (8, 2), (8, 1), (16, 8), (32, 8), (6, 2), (3, 1)])
+    nmax = max(lens)
+    si = r.choice([0, 1, 4, 4, 4, 15, 16, 20, nmax + 5])
+    sl = r.choice([0, 1, 32, 32, 32, 63, 64, 80, 81, 200])
+    last = r.choice([0, 1, 2, 64, 64, 64, 65, 129, 300, 513, nmax + 3])
+    mode = r.choice([0, 1, 1])
+    kernel = r.choice(["auto", "auto", "mma"])
+    scale = r.choice([128 ** -0.5, 0.05, 0.2])
+    return lens, hq, hkv, si, sl, last, mode, kernel, scale
+
+
+@pytest.mark.parametrize("seed", range(int(os.environ.get("TMX_FUZZ_SEEDS", "60"))))
+def test_attention_fuzz_vs_oracle(ops, seed):
+    lens, hq, hkv, si, sl, last, mode, kernel, scale = _fuzz_case(seed)
+    t = sum(lens)
+    q, k, v = _rand(t, hq, hkv, seed=1000 + seed)
+    cu_list = [0]
+    for n in lens:
+        cu_list.append(cu_list[-1] + n)
+    cu = torch.tensor(cu_list, dtype=torch.int32, device=DEV)
+    out = ops.prefill_attn(q.to(DEV), k.to(DEV), v.to(DEV), cu, max(lens), scale, si, sl, last, mode, kernel=kernel)
+    ref = orc.attention_varlen_fp32(q, k, v, cu_list, scale, si, sl, last, mode)
+    _check(out.cpu(), ref, (seed, lens, hq, hkv, si, sl, last, mode, kernel))

@@ -208,3 +208,47 @@ def test_qwen3_block_end_to_end(tmx, layer_idx):
     assert rep["violations"] == 0, rep
     close_enough(kv_cache[0].view(-1, hkv * d)[:t], wk, "k cache")
     assert torch.equal(kv_cache[1].view(-1, hkv * d)[:t].cpu(), v)
+
+
+@pytest.mark.parametrize("seed", range(int(os.environ.get("TMX_FUZZ_SEEDS", "30"))))
+def test_prologue_fuzz_vs_oracle(ops, seed):
+    """Random token counts, head counts, cache geometry, slot maps with padding, in place or not."""
+    import random
+    r = random.Random(seed)
+    d = 128
+    t = r.choice([1, 2, 7, 33, 64, 100, 257, 1000, r.randint(1, 3000)])
+    hq, hkv = r.choice([(1, 1), (2, 1), (4, 1), (4, 2), (8, 1), (8, 2), (16, 8), (32, 8), (5, 5), (7, 1), (64, 8)])
+    max_pos = r.choice([16, 4096, 40960])
+    bs = r.choice([16, 32, 48, 64])
+    nb = (t + bs - 1) // bs + r.randint(0, 3)
+    inplace, with_cache, hnd = r.random() < 0.5, r.random() < 0.7, r.random() < 0.3
+    qkv, qw, kw, pos = _inputs(t, hq, hkv, max_pos, seed=500 + seed)
+    cache = orc.cos_sin_cache(d, max_pos, r.choice([10000.0, 1000000.0]))
+    eps = r.choice([1e-6, 1e-5])
+    g = torch.Generator().manual_seed(seed)
+    slots = torch.randperm(bs * nb, generator=g)[:t].to(torch.int64)
+    slots[torch.rand(t, generator=g) < 0.1] = -1
+    q, k, v = qkv.split([hq * d, hkv * d, hkv * d], dim=-1)
+    wq, wk = orc.qk_norm_rope(q, k, pos, qw, kw, cache, eps, d)
+    shape = (2, nb, hkv, bs, d) if hnd else (2, nb, bs, hkv, d)
+    kv = torch.randn(shape, generator=g).bfloat16()
+    kv_d = kv.to(DEV)
+    kc, vc = kv_d.unbind(0)
+    if hnd:
+        kc, vc = kc.permute(0, 2, 1, 3), vc.permute(0, 2, 1, 3)
+    qkv_d = qkv.to(DEV)
+    qd, kd, vd = qkv_d.split([hq * d, hkv * d, hkv * d], dim=-1)
+    extra = dict(v=vd, key_cache=kc, value_cache=vc, slot_mapping=slots.to(DEV)) if with_cache else {}
+    gq, gk = ops.qk_norm_rope(pos.to(DEV), qd, kd, qw.to(DEV), kw.to(DEV), cache.to(DEV), eps, d, inplace=inplace,
+                              **extra)
+    torch.cuda.synchronize()
+    close_enough(gq, wq, "q")
+    close_enough(gk, wk, "k")
+    assert torch.equal(vd.cpu(), v)
+    want = kv.clone()
+    if with_cache:
+        wkc, wvc = want.unbind(0)
+        if hnd:
+            wkc, wvc = wkc.permute(0, 2, 1, 3), wvc.permute(0, 2, 1, 3)
+        orc.reshape_and_cache_flash(gk.cpu().view(t, hkv, d), v.reshape(t, hkv, d), wkc, wvc, slots)
+    assert torch.equal(kv_d.cpu(), want)          # written rows exact, every other slot untouched
