@@ -128,9 +128,19 @@ __device__ __forceinline__ uint64_t exp2_poly2(uint64_t t2) {
 // kSplitP: P is stored in two halves (keys [0,64) and [64,128) of the tile); the MMA warp issues
 // the first four k-steps of PV as soon as the first half is there, so that only HALF a PV (plus
 // the next score MMA) sits between the end of a group's exponentials and its next S tile.
-template <int kEmu, int kDbg, bool kTail, bool kSplitP>
+//
+// kSm == 2 (kPipe): the softmax pass software-pipelined across its four 32-column chunks.  In the
+// plain pass each chunk is a scheduling island between two tcgen05.wait::ld: ptxas interleaves its
+// MUFU.EX2 with the chunk's FMA-pipe work until that work runs out, and the last ~12 of the 24
+// MUFUs of every chunk then issue back to back at 8 clk each with nothing to hide behind (seen in
+// the SASS).  Here a chunk is split into A (mask, row max, t = x*scale - m) and B (exponentials,
+// row sum, bf16 pack), and each region between two waits holds B(c) next to A(c+1), through three
+// rotating 32-register score buffers.
+template <int kEmu, int kDbg, bool kTail, int kSm>
 __global__ void __launch_bounds__(kThreads, 1)
 attn_sm100_v3_kernel(const AttnParams p, const __grid_constant__ TmaMaps maps) {
+  constexpr bool kSplitP = (kSm == 1);
+  constexpr bool kPipe = (kSm == 2);
   extern __shared__ uint8_t smem_raw[];
   const uint32_t smem_base = (ptx::smem_u32(smem_raw) + 1023u) & ~1023u;   // SWIZZLE_128B: 1024-byte atoms
   const uint32_t sQ = smem_base, sRing = smem_base + kOffRing;
@@ -456,6 +466,111 @@ attn_sm100_v3_kernel(const AttnParams p, const __grid_constant__ TmaMaps maps) {
         }
         continue;
       }
+      if constexpr (kPipe) {
+        uint32_t pk[64];
+        uint64_t sum2;
+#pragma unroll 1
+        for (int attempt = 0;; ++attempt) {
+          const float neg_m = (m_ref == -INFINITY) ? 0.f : -m_ref;
+          const uint64_t negm2 = pk_f2(neg_m, neg_m);
+          float mx0 = -INFINITY, mx1 = -INFINITY;
+          sum2 = pk_f2(0.f, 0.f);
+          // A: raw scores of chunk c (in xr) -> t = x * scale - m_ref, in place; row max tracked
+          auto phase_a = [&](int c, uint32_t (&xr)[32]) {
+            float x[32];
+#pragma unroll
+            for (int e = 0; e < 32; ++e) x[e] = __uint_as_float(xr[e]);
+            if (!full) {
+              const int cb = c0 + c * 32;
+              const uint32_t bits = bm_row != nullptr ? bm_row[cb >> 5]
+                                                      : mask_word32(i, cb, n, lrow, p.si, p.sl, p.mode);
+#pragma unroll
+              for (int e = 0; e < 32; ++e) x[e] = ((bits >> e) & 1u) ? x[e] : -INFINITY;
+            }
+#pragma unroll
+            for (int e = 0; e < 32; e += 4) {
+              mx0 = fmaxf(mx0, fmaxf(x[e], x[e + 1]));
+              mx1 = fmaxf(mx1, fmaxf(x[e + 2], x[e + 3]));
+            }
+#pragma unroll
+            for (int e = 0; e < 32; e += 2) {
+              float a, b;
+              upk_f2(ffma2(pk_f2(x[e], x[e + 1]), sc2, negm2), a, b);
+              xr[e] = __float_as_uint(a);
+              xr[e + 1] = __float_as_uint(b);
+            }
+          };
+          // B: t of chunk c (in xr) -> probabilities, row sum, 16 packed bf16 pairs
+          auto phase_b = [&](int c, const uint32_t (&xr)[32]) {
+#pragma unroll
+            for (int e = 0; e < 32; e += 2) {
+              float a = __uint_as_float(xr[e]), b = __uint_as_float(xr[e + 1]);
+              uint64_t q2;
+              if ((e & 15) < kEmu) {
+                q2 = exp2_poly2(pk_f2(a, b));
+                upk_f2(q2, a, b);
+              } else {
+                a = fast_exp2(a);
+                b = fast_exp2(b);
+                q2 = pk_f2(a, b);
+              }
+              sum2 = fadd2(sum2, q2);
+              pk[c * 16 + e / 2] = pack2(a, b);
+            }
+          };
+          uint32_t b0[32], b1[32], b2[32];
+          ptx::tmem_ld32(tS, b0);
+          ptx::tc_wait_ld();
+          ptx::tmem_ld32(tS + 32, b1);
+          phase_a(0, b0);
+          ptx::tc_wait_ld();
+          ptx::tmem_ld32(tS + 64, b2);
+          phase_a(1, b1);
+          phase_b(0, b0);
+          ptx::tc_wait_ld();
+          ptx::tmem_ld32(tS + 96, b0);
+          phase_a(2, b2);
+          phase_b(1, b1);
+          ptx::tc_wait_ld();
+          phase_a(3, b0);
+          phase_b(2, b2);
+          const float m_new = fmaxf(m_ref, fmaxf(mx0, mx1) * sc);
+          const bool grow = (m_new > m_ref + 8.0f) || (m_ref == -INFINITY && m_new > -INFINITY);
+          if (attempt == 1 || !__any_sync(0xffffffffu, grow)) {
+            // every score has been read and the pass stands: the first half of P can go out
+            // while the last chunk is still being exponentiated
+            ptx::tmem_st32(tS, *reinterpret_cast<uint32_t(*)[32]>(&pk[0]));
+            phase_b(3, b0);
+            break;
+          }
+          if (j > 0) {
+            const float alpha = (m_new == -INFINITY) ? 1.0f : fast_exp2(m_ref - m_new);
+            l_run *= alpha;
+#pragma unroll
+            for (int c = 0; c < 4; ++c) {
+              uint32_t r[32];
+              ptx::tmem_ld32(tO + c * 32, r);
+              ptx::tc_wait_ld();
+#pragma unroll
+              for (int e = 0; e < 32; ++e) r[e] = __float_as_uint(__uint_as_float(r[e]) * alpha);
+              ptx::tmem_st32(tO + c * 32, r);
+            }
+            ptx::tc_wait_st();
+          }
+          m_ref = m_new;
+        }
+        {
+          float a, b;
+          upk_f2(sum2, a, b);
+          l_run += a + b;
+        }
+        ptx::tmem_st32(tS + 32, *reinterpret_cast<uint32_t(*)[32]>(&pk[32]));
+        ptx::tc_wait_st();
+        ptx::tc_fence_before();
+        __syncwarp();
+        if (lane == 0 && kDbg != 2) ptx::mbar_arrive(bar(bPReady + g));
+        continue;
+      }
       uint32_t pk[64];             // the row's 128 probabilities as bf16 pairs
       float mx;                    // row max of the raw scores of this tile
       uint64_t sum2;               // two partial row sums
@@ -700,6 +815,12 @@ int launch_attn_sm100_v3(const AttnParams& p, int variant, cudaStream_t s) {
     static const Kern split[4] = {attn_sm100_v3_kernel<4, 0, false, true>, attn_sm100_v3_kernel<0, 0, false, true>,
                                   attn_sm100_v3_kernel<6, 0, false, true>, attn_sm100_v3_kernel<8, 0, false, true>};
     kern = split[emu];
+  }
+  // TMX_SM100_VARIANT bit 6: softmax pass pipelined across its chunks (kSm == 2)
+  if (dbg == 0 && (variant & 64)) {
+    static const Kern pipe[4] = {attn_sm100_v3_kernel<4, 0, false, 2>, attn_sm100_v3_kernel<0, 0, false, 2>,
+                                 attn_sm100_v3_kernel<6, 0, false, 2>, attn_sm100_v3_kernel<8, 0, false, 2>};
+    kern = pipe[emu];
   }
   TMX_CUDA_TRY(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, kSmem));
   TmaMaps maps;
