@@ -136,11 +136,22 @@ __device__ __forceinline__ uint64_t exp2_poly2(uint64_t t2) {
 // the SASS).  Here a chunk is split into A (mask, row max, t = x*scale - m) and B (exponentials,
 // row sum, bf16 pack), and each region between two waits holds B(c) next to A(c+1), through three
 // rotating 32-register score buffers.
+//
+// kSm == 3 (kAhead): kPipe + the score MMA of a tile issued as two 64-key halves H0 | H1 living in
+// the two 64-column blocks of the group's S buffer, the blocks swapping roles every tile:
+//   tile j:  H0(j) in block j&1, H1(j) in the other; P(j) (64 columns) overwrites H0(j)'s block.
+// The block of H1(j) is free as soon as the softmax pass has loaded it and knows it will not redo
+// the pass (row max is known after phase A of the last chunk, ~60 % into the pass), so H0(j+1) is
+// issued THEN -- before P(j) exists -- and H1(j+1) follows PV(j) into P(j)'s block.  The next
+// pass starts on H0(j+1) right after its P store and needs H1(j+1) only half-way through, which
+// takes most of PV(j) + S(j+1) out of the per-group chain softmax -> P -> PV -> S -> softmax.
+// Barriers: bPV0Done = "H0 ready", bSFull = "H1 ready", bP1Ready = "H1's block free".
 template <int kEmu, int kDbg, bool kTail, int kSm>
 __global__ void __launch_bounds__(kThreads, 1)
 attn_sm100_v3_kernel(const AttnParams p, const __grid_constant__ TmaMaps maps) {
   constexpr bool kSplitP = (kSm == 1);
-  constexpr bool kPipe = (kSm == 2);
+  constexpr bool kAhead = (kSm == 3);
+  constexpr bool kPipe = (kSm == 2) || kAhead;
   extern __shared__ uint8_t smem_raw[];
   const uint32_t smem_base = (ptx::smem_u32(smem_raw) + 1023u) & ~1023u;   // SWIZZLE_128B: 1024-byte atoms
   const uint32_t sQ = smem_base, sRing = smem_base + kOffRing;
@@ -291,11 +302,76 @@ attn_sm100_v3_kernel(const AttnParams p, const __grid_constant__ TmaMaps maps) {
                     acc || ks > 0);
     };
 
+    // kAhead: half h (64 keys) of S_g for tile j into column block (j & 1) ^ h
+    constexpr uint32_t kIdescS64 = ptx::instr_desc_bf16(128, 64, false);
+    auto issue_s_half = [&](int g, int st, int j, int h) {
+      const uint32_t d_tmem = tb + kColS + (uint32_t)(g * 128) + (uint32_t)((((j & 1) ^ h)) * 64);
+      const uint64_t qa = dQ + (uint64_t)((g * 2 * (kBM * 128)) >> 4);
+      const uint64_t kb = dK + (uint64_t)((st * kTileBytes + h * 64 * 128) >> 4);   // keys 64h.. of the tile
+#pragma unroll
+      for (int ks = 0; ks < 8; ++ks) {
+        const uint32_t qo = ((ks >> 2) * (kBM * 128) + (ks & 3) * 32) >> 4;
+        const uint32_t ko = ((ks >> 2) * kPanelBytes + (ks & 3) * 32) >> 4;
+        ptx::mma_ss(d_tmem, qa + qo, kb + ko, kIdescS64, ks > 0);
+      }
+    };
+    auto issue_pv_blk = [&](int g, int st, bool acc, int j) {     // P(j) sits in block j & 1
+      const uint32_t d_tmem = tb + kColO + (uint32_t)(g * 128);
+      const uint32_t a_tmem = tb + kColS + (uint32_t)(g * 128) + (uint32_t)((j & 1) * 64);
+      const uint64_t vb = dV + (uint64_t)((st * kTileBytes) >> 4);
+#pragma unroll
+      for (int ks = 0; ks < kBN / 16; ++ks)
+        ptx::mma_ts(d_tmem, a_tmem + (uint32_t)(ks * 8), vb + (uint64_t)((ks * 2048) >> 4), kIdescO,
+                    acc || ks > 0);
+    };
+
     int st = 0, ph = 0;                               // ring position of the next item to consume
     auto advance = [&] { if (++st == kStages) { st = 0; ph ^= 1; } };
     ptx::mbar_wait(bar(bQFull), 0);
     ptx::mbar_wait(bar(bFull + 0), 0);                // K(0)
     ptx::tc_fence_after();
+    if constexpr (kAhead) {
+      if (ptx::elect_one()) {
+        for (int g = 0; g < 2; ++g) {
+          issue_s_half(g, 0, 0, 0); ptx::mma_commit(bar(bPV0Done + g));
+          issue_s_half(g, 0, 0, 1); ptx::mma_commit(bar(bSFull + g));
+        }
+        ptx::mma_commit(bar(bEmpty + 0));
+      }
+      __syncwarp();
+      advance();
+      for (int j = 0; j < ntot; ++j) {
+        const int vst = st, vph = ph;
+        advance();
+        const int kst = st, kph = ph;
+        const bool more = j + 1 < ntot;
+        if (more) advance();
+        ptx::mbar_wait(bar(bFull + vst), vph);
+#pragma unroll
+        for (int g = 0; g < 2; ++g) {
+          if (more) {
+            if (g == 0) ptx::mbar_wait(bar(bFull + kst), kph);
+            ptx::mbar_wait(bar(bP1Ready + g), j & 1);           // H1(j)'s block has been read
+            ptx::tc_fence_after();
+            if (ptx::elect_one()) { issue_s_half(g, kst, j + 1, 0); ptx::mma_commit(bar(bPV0Done + g)); }
+            __syncwarp();
+          }
+          ptx::mbar_wait(bar(bPReady + g), j & 1);
+          ptx::tc_fence_after();
+          if (ptx::elect_one()) {
+            issue_pv_blk(g, vst, j > 0, j);
+            if (!more) ptx::mma_commit(bar(bOFull + g));
+            if (g == 1) ptx::mma_commit(bar(bEmpty + vst));
+            if (more) {
+              issue_s_half(g, kst, j + 1, 1);                   // into P(j)'s block, behind PV(j)
+              ptx::mma_commit(bar(bSFull + g));
+              if (g == 1) ptx::mma_commit(bar(bEmpty + kst));
+            }
+          }
+          __syncwarp();
+        }
+      }
+    } else {
     if (ptx::elect_one()) {
       issue_s(0, 0); ptx::mma_commit(bar(bSFull + 0));
       if (kDbg != 3) { issue_s(1, 0); ptx::mma_commit(bar(bSFull + 1)); }
@@ -353,6 +429,7 @@ attn_sm100_v3_kernel(const AttnParams p, const __grid_constant__ TmaMaps maps) {
         }
       }
     }
+    }   // !kAhead
   } else {
     // =========================== softmax groups ===========================
     const int g = warp >> 2;                       // 0: head h0, 1: head h0 + 1
@@ -370,7 +447,8 @@ attn_sm100_v3_kernel(const AttnParams p, const __grid_constant__ TmaMaps maps) {
     const uint64_t sc2 = pk_f2(sc, sc);
 
     for (int j = 0; j < total && kDbg != 1 && !(kDbg == 3 && g == 1); ++j) {
-      ptx::mbar_wait(bar(bSFull + g), kDbg == 2 ? 0 : (j & 1));
+      if constexpr (kAhead) ptx::mbar_wait(bar(bPV0Done + g), j & 1);          // first 64 keys of S(j)
+      else ptx::mbar_wait(bar(bSFull + g), kDbg == 2 ? 0 : (j & 1));
       ptx::tc_fence_after();
       const int c0 = tile_of(j) * kBN;
       const bool full = bm_row == nullptr &&
@@ -469,6 +547,9 @@ attn_sm100_v3_kernel(const AttnParams p, const __grid_constant__ TmaMaps maps) {
       if constexpr (kPipe) {
         uint32_t pk[64];
         uint64_t sum2;
+        // column blocks of this tile's two 64-key halves (kAhead: they swap every tile); P goes to H0's
+        const uint32_t tH0 = kAhead ? tS + (uint32_t)((j & 1) * 64) : tS;
+        const uint32_t tH1 = kAhead ? tS + (uint32_t)(((j & 1) ^ 1) * 64) : tS + 64;
 #pragma unroll 1
         for (int attempt = 0;; ++attempt) {
           const float neg_m = (m_ref == -INFINITY) ? 0.f : -m_ref;
@@ -519,16 +600,20 @@ attn_sm100_v3_kernel(const AttnParams p, const __grid_constant__ TmaMaps maps) {
             }
           };
           uint32_t b0[32], b1[32], b2[32];
-          ptx::tmem_ld32(tS, b0);
+          ptx::tmem_ld32(tH0, b0);
           ptx::tc_wait_ld();
-          ptx::tmem_ld32(tS + 32, b1);
+          ptx::tmem_ld32(tH0 + 32, b1);
           phase_a(0, b0);
           ptx::tc_wait_ld();
-          ptx::tmem_ld32(tS + 64, b2);
+          if constexpr (kAhead) {                     // keys 64..127 of S(j) (done already on a redo)
+            ptx::mbar_wait(bar(bSFull + g), j & 1);
+            ptx::tc_fence_after();
+          }
+          ptx::tmem_ld32(tH1, b2);
           phase_a(1, b1);
           phase_b(0, b0);
           ptx::tc_wait_ld();
-          ptx::tmem_ld32(tS + 96, b0);
+          ptx::tmem_ld32(tH1 + 32, b0);
           phase_a(2, b2);
           phase_b(1, b1);
           ptx::tc_wait_ld();
@@ -537,9 +622,14 @@ attn_sm100_v3_kernel(const AttnParams p, const __grid_constant__ TmaMaps maps) {
           const float m_new = fmaxf(m_ref, fmaxf(mx0, mx1) * sc);
           const bool grow = (m_new > m_ref + 8.0f) || (m_ref == -INFINITY && m_new > -INFINITY);
           if (attempt == 1 || !__any_sync(0xffffffffu, grow)) {
+            if constexpr (kAhead) {                   // H1(j)'s block is read and will not be re-read
+              ptx::tc_fence_before();
+              __syncwarp();
+              if (lane == 0) ptx::mbar_arrive(bar(bP1Ready + g));
+            }
             // every score has been read and the pass stands: the first half of P can go out
             // while the last chunk is still being exponentiated
-            ptx::tmem_st32(tS, *reinterpret_cast<uint32_t(*)[32]>(&pk[0]));
+            ptx::tmem_st32(tH0, *reinterpret_cast<uint32_t(*)[32]>(&pk[0]));
             phase_b(3, b0);
             break;
           }
@@ -564,7 +654,7 @@ attn_sm100_v3_kernel(const AttnParams p, const __grid_constant__ TmaMaps maps) {
           upk_f2(sum2, a, b);
           l_run += a + b;
         }
-        ptx::tmem_st32(tS + 32, *reinterpret_cast<uint32_t(*)[32]>(&pk[32]));
+        ptx::tmem_st32(tH0 + 32, *reinterpret_cast<uint32_t(*)[32]>(&pk[32]));
         ptx::tc_wait_st();
         ptx::tc_fence_before();
         __syncwarp();
@@ -817,10 +907,13 @@ int launch_attn_sm100_v3(const AttnParams& p, int variant, cudaStream_t s) {
     kern = split[emu];
   }
   // TMX_SM100_VARIANT bit 6: softmax pass pipelined across its chunks (kSm == 2)
+  // bits 6 + 4 together (80): kSm == 3, pipelined pass + score MMA in two 64-key halves issued ahead
   if (dbg == 0 && (variant & 64)) {
     static const Kern pipe[4] = {attn_sm100_v3_kernel<4, 0, false, 2>, attn_sm100_v3_kernel<0, 0, false, 2>,
                                  attn_sm100_v3_kernel<6, 0, false, 2>, attn_sm100_v3_kernel<8, 0, false, 2>};
-    kern = pipe[emu];
+    static const Kern ahead[4] = {attn_sm100_v3_kernel<4, 0, false, 3>, attn_sm100_v3_kernel<0, 0, false, 3>,
+                                  attn_sm100_v3_kernel<6, 0, false, 3>, attn_sm100_v3_kernel<8, 0, false, 3>};
+    kern = (variant & 16) ? ahead[emu] : pipe[emu];
   }
   TMX_CUDA_TRY(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, kSmem));
   TmaMaps maps;
