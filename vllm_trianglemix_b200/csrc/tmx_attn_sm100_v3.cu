@@ -605,17 +605,26 @@ attn_sm100_v3_kernel(const AttnParams p, const __grid_constant__ TmaMaps maps) {
           ptx::tmem_ld32(tH0 + 32, b1);
           phase_a(0, b0);
           ptx::tc_wait_ld();
-          if constexpr (kAhead) {                     // keys 64..127 of S(j) (done already on a redo)
-            ptx::mbar_wait(bar(bSFull + g), j & 1);
+          if constexpr (kAhead) {
+            // everything that only needs H0 first (half of the pass), then wait for keys 64..127
+            phase_a(1, b1);
+            phase_b(0, b0);
+            phase_b(1, b1);
+            ptx::mbar_wait(bar(bSFull + g), j & 1);   // (completed long ago on a redo)
             ptx::tc_fence_after();
+            ptx::tmem_ld32(tH1, b2);
+            ptx::tc_wait_ld();
+            ptx::tmem_ld32(tH1 + 32, b0);
+            phase_a(2, b2);
+          } else {
+            ptx::tmem_ld32(tH1, b2);
+            phase_a(1, b1);
+            phase_b(0, b0);
+            ptx::tc_wait_ld();
+            ptx::tmem_ld32(tH1 + 32, b0);
+            phase_a(2, b2);
+            phase_b(1, b1);
           }
-          ptx::tmem_ld32(tH1, b2);
-          phase_a(1, b1);
-          phase_b(0, b0);
-          ptx::tc_wait_ld();
-          ptx::tmem_ld32(tH1 + 32, b0);
-          phase_a(2, b2);
-          phase_b(1, b1);
           ptx::tc_wait_ld();
           phase_a(3, b0);
           phase_b(2, b2);
