@@ -163,7 +163,9 @@ int tmx_prefill_attn(void* out, const void* q, const void* k, const void* v,
  * (covers FlashAttention's [2, num_blocks, block_size, Hkv, D] NHD layout,
  * flash_attn.py:78-87, and the HND permutation), bf16 cache only ("auto" kv_cache_dtype).
  * D must be 128; all strides multiples of 8 elements, pointers 16-byte aligned.
- * v / k_cache / v_cache / slot_mapping may all be null (no cache write). */
+ * v / k_cache / v_cache / slot_mapping may all be null (no cache write).
+ * positions[t] must lie in [0, max_pos): like the reference's CUDA rotary kernel
+ * (csrc/pos_encoding_kernels.cu) the device code does not check it. */
 int tmx_qk_norm_rope(void* q_out, void* k_out, const void* q, const void* k,
                      const void* q_weight, const void* k_weight, const int64_t* positions,
                      const void* cos_sin_cache, int max_pos, int T, int Hq, int Hkv, int D,

@@ -4,11 +4,15 @@ golden vectors.
 
 Tolerance (stated, floating point): every operation of the reference's forward_native is
 reproduced with its bf16 rounding, so the only freedom is the fp32 summation order of the 128
-squares in the variance.  That can move rsqrt by 1 fp32 ulp, which flips a bf16 rounding for
-about 1 element in 2^8..2^16; such a flip is 1 bf16 ulp and RoPE's two rounded products can carry
-it to 2 ulp of the larger operand.  Bar: >= 99.5 % of elements bit-identical, the rest within
-atol 1.5e-2 / rtol 1e-2 (the attention bar) of the oracle.  Cache rows and untouched slots:
-bit-exact."""
+squares in the variance.  That can move a head row's rsqrt by 1 fp32 ulp, which flips the bf16
+rounding of x * rsqrt only for elements sitting within 1 fp32 ulp of a rounding midpoint (about
+1 in 2^15; equal |x| values flip together) -- measured: a flipped row is seen in ~0.1 % of head
+rows, e.g. fuzz seed 1385, reproduced on the CPU by adding 1 ulp to the sum of squares.  A flip is
+1 bf16 ulp of a rotation operand, which x1*cos - x2*sin carries into an output that may be much
+smaller than the operand (fuzz seed 1858: |diff| 2^-5 next to operands of 4..8).  Bar: every
+element within atol 1.5e-2 + rtol 1e-2 x |rotary pair (e, e+64)| of the oracle, and at most
+max(2, 1 %) of the head rows (128 elements) contain any element that is not bit-identical.
+Cache rows and untouched slots: bit-exact."""
 import os
 
 import numpy as np
@@ -41,12 +45,16 @@ def bf(a):
 
 def close_enough(got, want, what):
     got, want = got.cpu(), want.cpu()
-    same = (got.view(torch.int16) == want.view(torch.int16)).float().mean().item()
-    assert same >= 0.995, "%s: only %.4f of elements bit-identical" % (what, same)
-    g, w = got.float(), want.float()
-    bad = ((g - w).abs() > 1.5e-2 + 1e-2 * w.abs()).sum().item()
+    ne = (got.reshape(-1, 128).view(torch.int16) != want.reshape(-1, 128).view(torch.int16))
+    rows, rows_bad = ne.shape[0], int(ne.any(dim=1).sum())
+    assert rows_bad <= max(2, rows // 100), "%s: %d of %d head rows differ from the oracle" % (what, rows_bad, rows)
+    # a flip is 1 bf16 ulp of a ROTATION OPERAND, so the relative part is taken against the norm of the
+    # rotary pair (e, e + 64) the element belongs to, not against the element (x1*cos - x2*sin may cancel)
+    g, w = got.float().reshape(-1, 2, 64), want.float().reshape(-1, 2, 64)
+    pair = (w * w).sum(dim=1, keepdim=True).sqrt()
+    bad = ((g - w).abs() > 1.5e-2 + 1e-2 * pair).sum().item()
     assert bad == 0, "%s: %d elements outside tolerance (max abs %.3e)" % (what, bad, (g - w).abs().max().item())
-    return same
+    return 1.0 - float(ne.float().mean())
 
 
 @pytest.mark.parametrize("tag", ["a", "b"])
