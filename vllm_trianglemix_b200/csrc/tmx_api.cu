@@ -216,7 +216,7 @@ extern "C" int tmx_prefill_attn(void* out, const void* q, const void* k, const v
   if (st != TMX_OK) return st;
   if (pl.kernel == TMX_KERNEL_TCGEN05) {
     const int var = sm100_variant();
-    return sm100_use_v2(var) ? launch_attn_sm100(p, var & 15, s) : launch_attn_sm100_v3(p, var & (31 | 64), s);
+    return sm100_use_v2(var) ? launch_attn_sm100(p, var & 15, s) : launch_attn_sm100_v3(p, var & 127, s);
   }
   return launch_attn_mma(p, pl.bm, s);
 }

@@ -22,6 +22,7 @@
 //
 // Replaces vllm/attention/ascend_trianglemix.py:86-106 of the reference for dense-causal
 // layers (and for any triangle setting through the same block index).
+#include <cstdlib>
 #include "tmx_attn.cuh"
 #include "tmx_sm100_ptx.cuh"
 #include "tmx_tma.cuh"
@@ -150,7 +151,8 @@ template <int kEmu, int kDbg, bool kTail, int kSm>
 __global__ void __launch_bounds__(kThreads, 1)
 attn_sm100_v3_kernel(const AttnParams p, const __grid_constant__ TmaMaps maps) {
   constexpr bool kSplitP = (kSm == 1);
-  constexpr bool kAhead = (kSm == 3);
+  constexpr bool kAhead = (kSm == 3) || (kSm == 4);
+  constexpr bool kPoll = (kSm == 4);   // kAhead with an event-driven MMA issuer (each group advances on its own)
   constexpr bool kPipe = (kSm == 2) || kAhead;
   extern __shared__ uint8_t smem_raw[];
   const uint32_t smem_base = (ptx::smem_u32(smem_raw) + 1023u) & ~1023u;   // SWIZZLE_128B: 1024-byte atoms
@@ -340,6 +342,59 @@ attn_sm100_v3_kernel(const AttnParams p, const __grid_constant__ TmaMaps maps) {
       }
       __syncwarp();
       advance();
+      if constexpr (kPoll) {
+        // Ring item 0 = K(0); tile j: V(j) = item 1 + 2j, K(j+1) = item 2 + 2j.  Each group walks its own
+        // tile counter; an item's stage is released by whichever group finishes with it second (a commit
+        // covers every MMA this thread issued before it).
+        int jg[2] = {0, 0}, stage[2] = {0, 0}, cons[2] = {1, 1};   // stage 0: H0 of tile j+1 pending, 1: PV of tile j
+        auto test = [&](int b, int parity) {
+          return __shfl_sync(0xffffffffu, (int)ptx::mbar_test(bar(b), (uint32_t)parity), 0) != 0;
+        };
+        auto item_full = [&](int item) { return test(bFull + item % kStages, (item / kStages) & 1); };
+        uint32_t idle = 0;
+        while (jg[0] < ntot || jg[1] < ntot) {
+          bool progress = false;
+#pragma unroll
+          for (int g = 0; g < 2; ++g) {
+            const int j = jg[g];
+            if (j >= ntot) continue;
+            const bool more = j + 1 < ntot;
+            const int vitem = 1 + 2 * j, kitem = 2 + 2 * j;
+            if (more && stage[g] == 0) {
+              if (test(bP1Ready + g, j & 1) && item_full(kitem)) {        // H1(j)'s block has been read
+                ptx::tc_fence_after();
+                if (ptx::elect_one()) {
+                  issue_s_half(g, kitem % kStages, j + 1, 0);
+                  ptx::mma_commit(bar(bPV0Done + g));
+                }
+                __syncwarp();
+                stage[g] = 1;
+                progress = true;
+              }
+            }
+            if ((!more || stage[g] == 1) && test(bPReady + g, j & 1) && item_full(vitem)) {
+              ptx::tc_fence_after();
+              if (ptx::elect_one()) {
+                issue_pv_blk(g, vitem % kStages, j > 0, j);
+                if (!more) ptx::mma_commit(bar(bOFull + g));
+                if (cons[g ^ 1] > vitem) ptx::mma_commit(bar(bEmpty + vitem % kStages));
+                if (more) {
+                  issue_s_half(g, kitem % kStages, j + 1, 1);             // into P(j)'s block, behind PV(j)
+                  ptx::mma_commit(bar(bSFull + g));
+                  if (cons[g ^ 1] > kitem) ptx::mma_commit(bar(bEmpty + kitem % kStages));
+                }
+              }
+              __syncwarp();
+              cons[g] = (more ? kitem : vitem) + 1;
+              jg[g] = j + 1;
+              stage[g] = 0;
+              progress = true;
+            }
+          }
+          if (progress) idle = 0;
+          else { __nanosleep(32); if (++idle > (1u << 24)) __trap(); }
+        }
+      } else
       for (int j = 0; j < ntot; ++j) {
         const int vst = st, vph = ph;
         advance();
@@ -922,7 +977,17 @@ int launch_attn_sm100_v3(const AttnParams& p, int variant, cudaStream_t s) {
                                  attn_sm100_v3_kernel<6, 0, false, 2>, attn_sm100_v3_kernel<8, 0, false, 2>};
     static const Kern ahead[4] = {attn_sm100_v3_kernel<4, 0, false, 3>, attn_sm100_v3_kernel<0, 0, false, 3>,
                                   attn_sm100_v3_kernel<6, 0, false, 3>, attn_sm100_v3_kernel<8, 0, false, 3>};
-    kern = (variant & 16) ? ahead[emu] : pipe[emu];
+    static const Kern poll[4] = {attn_sm100_v3_kernel<4, 0, false, 4>, attn_sm100_v3_kernel<0, 0, false, 4>,
+                                 attn_sm100_v3_kernel<6, 0, false, 4>, attn_sm100_v3_kernel<8, 0, false, 4>};
+    // bits 6 + 5 + 4 (112): kSm == 4, the look-ahead kernel with an event-driven MMA issuer
+    kern = (variant & 16) ? ((variant & 32) ? poll[emu] : ahead[emu]) : pipe[emu];
+  }
+  // Default (no switch set): the look-ahead kernel with every exponential on MUFU (== switch value 81),
+  // measured +1.2 % over the classic single-MMA-per-tile kernel at 128K (1123 vs 1110 TFLOP/s, four
+  // alternating pairs, profiles/r01_sm100_v3_experiments.md section 7).  TMX_SM100_CLASSIC=1 keeps the classic one.
+  if (variant == 0) {
+    static const bool classic = [] { const char* e = std::getenv("TMX_SM100_CLASSIC"); return e && std::atoi(e) != 0; }();
+    if (!classic) kern = attn_sm100_v3_kernel<0, 0, false, 3>;
   }
   TMX_CUDA_TRY(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, kSmem));
   TmaMaps maps;
