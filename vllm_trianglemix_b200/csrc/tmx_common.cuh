@@ -163,8 +163,19 @@ void set_cuda_error(cudaError_t e, const char* where);
     }                                                        \
   } while (0)
 
+// Per-device caches (tmx_api.cu), keyed by cudaGetDevice(): one process may drive several GPUs.
 int device_sm_count();
 int check_arch();  // TMX_OK or TMX_ERR_ARCH / TMX_ERR_CUDA
+// Has cudaFuncAttributeMaxDynamicSharedMemorySize >= smem already been set for kernel `slot`
+// on the CURRENT device?  (function attributes are per device.)  Records the new size if not.
+enum { kAttrV3Dense = 0, kAttrV3Tail, kAttrV3Pair, kAttrMma64, kAttrMma128, kAttrStream3 /* + nW/16 */,
+       kAttrGemm = kAttrStream3 + 8, kAttrSlots = kAttrGemm + 4 };
+bool smem_attr_cached(int slot, int smem);
+#define TMX_SET_SMEM_ATTR(kern, slot, smem)                                                        \
+  do {                                                                                             \
+    if (!::tmx::smem_attr_cached((slot), (smem)))                                                  \
+      TMX_CUDA_TRY(cudaFuncSetAttribute((kern), cudaFuncAttributeMaxDynamicSharedMemorySize, (smem))); \
+  } while (0)
 void count_launch(int n = 1);
 void reset_launch_count();
 

@@ -24,10 +24,38 @@ inline PFN_cuTensorMapEncodeTiled_v12000 tma_encode_fn() {
   return fn;
 }
 
+// Descriptor cache: a CUtensorMap is a pure function of (base, dims, pitch, box), and a serving
+// loop calls every layer with the same handful of buffers, so the 3-6 driver encode calls per
+// tmx_prefill_attn are served from a small per-thread table instead (SURVEY 8(b) "Ownership":
+// the library keeps nothing but cached descriptors / attributes).
+struct TmaKey {
+  const void* base; long long a, b, c; int d, e, kind;
+  bool operator==(const TmaKey& o) const {
+    return base == o.base && a == o.a && b == o.b && c == o.c && d == o.d && e == o.e && kind == o.kind;
+  }
+};
+struct TmaCache {
+  static constexpr int kEntries = 64;
+  TmaKey keys[kEntries];
+  CUtensorMap maps[kEntries];
+  int used = 0, next = 0;
+  const CUtensorMap* find(const TmaKey& k) const {
+    for (int i = 0; i < used; ++i) if (keys[i] == k) return &maps[i];
+    return nullptr;
+  }
+  void put(const TmaKey& k, const CUtensorMap& m) {
+    const int i = used < kEntries ? used++ : (next++ % kEntries);
+    keys[i] = k; maps[i] = m;
+  }
+};
+inline TmaCache& tma_cache() { static thread_local TmaCache c; return c; }
+
 // [rows][cols] bf16 row-major with a row pitch of `pitch_elems`; box = 64 columns x box_rows,
 // 128-byte swizzle, out-of-bounds rows read as zero.
 inline int tma_map_2d(CUtensorMap* m, const void* base, long long rows, long long cols,
                       long long pitch_elems, int box_rows) {
+  const TmaKey key{base, rows, cols, pitch_elems, box_rows, 0, 2};
+  if (const CUtensorMap* hit = tma_cache().find(key)) { *m = *hit; return TMX_OK; }
   auto enc = tma_encode_fn();
   if (!enc) return TMX_ERR_CUDA;
   cuuint64_t dims[2] = {(cuuint64_t)cols, (cuuint64_t)rows};
@@ -41,12 +69,15 @@ inline int tma_map_2d(CUtensorMap* m, const void* base, long long rows, long lon
     set_cuda_error(cudaErrorInvalidValue, "cuTensorMapEncodeTiled");
     return TMX_ERR_CUDA;
   }
+  tma_cache().put(key, *m);
   return TMX_OK;
 }
 
 // [T][H][128] bf16 viewed as (d, head, token); box = 64 d x G heads x TT tokens, 128-byte swizzle
 inline int tma_map_q3d(CUtensorMap* m, const void* base, long long tokens, int heads, long long pitch_elems, int G,
                 int TT) {
+  const TmaKey key{base, tokens, (long long)heads, pitch_elems, G, TT, 3};
+  if (const CUtensorMap* hit = tma_cache().find(key)) { *m = *hit; return TMX_OK; }
   auto enc = tma_encode_fn();
   if (!enc) return TMX_ERR_CUDA;
   cuuint64_t dims[3] = {(cuuint64_t)128, (cuuint64_t)heads, (cuuint64_t)tokens};
@@ -60,6 +91,7 @@ inline int tma_map_q3d(CUtensorMap* m, const void* base, long long tokens, int h
     set_cuda_error(cudaErrorInvalidValue, "cuTensorMapEncodeTiled(q3d)");
     return TMX_ERR_CUDA;
   }
+  tma_cache().put(key, *m);
   return TMX_OK;
 }
 
