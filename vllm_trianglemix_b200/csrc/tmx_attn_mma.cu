@@ -101,7 +101,7 @@ __global__ void __launch_bounds__(BM * 2, (BM == 64 ? 3 : 1)) attn_mma_kernel(co
   } else if ((int)blockIdx.x < p.n_slots) {
     const SlotInfo s = p.slots[p.n_slots - 1 - blockIdx.x];   // descending: longest first
     if (s.seq < 0 || s.nsplit > 0) return;
-    seq = s.seq; n = s.n; r0 = s.q_tile * BM;
+    seq = s.seq; n = s.n; r0 = seq_geom(p, seq).ctx + s.q_tile * BM;   // absolute row (context + chunk)
     lo0 = s.lo0; hi0 = s.hi0; lo1 = s.lo1; hi1 = s.hi1;
   } else {
     // split-KV worker: e -> (sequence, which of the last tiles, chunk)
@@ -122,32 +122,44 @@ __global__ void __launch_bounds__(BM * 2, (BM == 64 ? 3 : 1)) attn_mma_kernel(co
     lo1 = hi1 = 0;
     part = (seq * p.last_tiles + ql) * p.nsplit_max + chunk;
   }
-  const int seq_start = p.cu[seq];
-  const int r1 = min(n, r0 + BM) - 1;
+  const SeqGeom gm = seq_geom(p, seq);
+  const int seq_start = gm.q_start - gm.ctx;          // query-buffer row of absolute row 0
   const int lrow = first_dense_row(n, p.last);
+  int r1 = min(n, r0 + BM) - 1;
+  if (p.tail_clip && p.mode == TMX_MODE_TRIANGLE && lrow < n) r1 = min(r1, lrow - 1);
   const int cnt0 = hi0 - lo0, total = cnt0 + (hi1 - lo1);
 
   const __nv_bfloat16* qg = p.q + (long long)(seq_start + r0) * p.q_stride + head * kD;
-  const __nv_bfloat16* kg = p.k + (long long)seq_start * p.kv_stride + kvh * kD;
-  const __nv_bfloat16* vg = p.v + (long long)seq_start * p.kv_stride + kvh * kD;
+  const __nv_bfloat16* kg = p.k + (long long)gm.k_start * p.kv_stride + kvh * kD;
+  const __nv_bfloat16* vg = p.v + (long long)gm.k_start * p.kv_stride + kvh * kD;
+  const int* pages = p.block_table ? p.block_table + (long long)seq * p.bt_stride : nullptr;
 
   auto tile_of = [&](int it) { return it < cnt0 ? lo0 + it : lo1 + (it - cnt0); };
+  // 64 keys x 128 d of K or V into a swizzled tile; keys >= n are zero-filled.  Paged cache:
+  // key j lives at slot pages[j / page_size] * page_size + j % page_size.
+  auto load_kv_tile = [&](uint32_t sdst, const __nv_bfloat16* base, int tile) {
+    const int valid = min(kBN, n - tile * kBN);
+    if (pages == nullptr) {
+      load_tile<kThreads>(sdst, base + (long long)tile * kBN * p.kv_stride, p.kv_stride, kBN, valid, tid);
+      return;
+    }
+    for (int c = tid; c < kBN * 16; c += kThreads) {
+      const int r = c >> 4, ch = c & 15;
+      const bool ok = r < valid;
+      const int key = tile * kBN + (ok ? r : 0);
+      const long long slot = (long long)pages[key / p.page_size] * p.page_size + key % p.page_size;
+      cp_async16(sdst + swz(r, ch), base + slot * p.kv_stride + ch * 8, ok);
+    }
+  };
   auto issue_kv = [&](int it) {
-    int tile = tile_of(it), st = it & 1;
-    int valid = min(kBN, n - tile * kBN);
-    load_tile<kThreads>(sK + st * kTileBytes, kg + (long long)tile * kBN * p.kv_stride, p.kv_stride,
-                        kBN, valid, tid);
-    load_tile<kThreads>(sV + st * kTileBytes, vg + (long long)tile * kBN * p.kv_stride, p.kv_stride,
-                        kBN, valid, tid);
+    const int tile = tile_of(it), st = it & 1;
+    load_kv_tile(sK + st * kTileBytes, kg, tile);
+    load_kv_tile(sV + st * kTileBytes, vg, tile);
   };
 
   // ---- prologue: Q through the V region, K tile 0 alongside ------------------
   load_tile<kThreads>(sV, qg, p.q_stride, BM, r1 - r0 + 1, tid);
-  {
-    int tile = tile_of(0);
-    load_tile<kThreads>(sK, kg + (long long)tile * kBN * p.kv_stride, p.kv_stride, kBN,
-                        min(kBN, n - tile * kBN), tid);
-  }
+  load_kv_tile(sK, kg, tile_of(0));
   cp_async_commit();
   cp_async_wait<0>();
   __syncthreads();
@@ -159,11 +171,7 @@ __global__ void __launch_bounds__(BM * 2, (BM == 64 ? 3 : 1)) attn_mma_kernel(co
       ldsm_x4(sV + swz(row, 2 * ks + (lane >> 4)), qa[ks][0], qa[ks][1], qa[ks][2], qa[ks][3]);
   }
   __syncthreads();
-  {
-    int tile = tile_of(0);
-    load_tile<kThreads>(sV, vg + (long long)tile * kBN * p.kv_stride, p.kv_stride, kBN,
-                        min(kBN, n - tile * kBN), tid);
-  }
+  load_kv_tile(sV, vg, tile_of(0));
   cp_async_commit();
 
   float o[16][4];
@@ -392,12 +400,8 @@ __global__ void __launch_bounds__(256) combine_kernel(const AttnParams p) {
 
 template <int BM>
 int launch_attn_mma_t(const AttnParams& p, cudaStream_t s) {
-  static bool attr_set = false;
   constexpr int smem = 4 * kTileBytes;
-  if (!attr_set) {
-    TMX_CUDA_TRY(cudaFuncSetAttribute(attn_mma_kernel<BM>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
-    attr_set = true;
-  }
+  TMX_SET_SMEM_ATTR(attn_mma_kernel<BM>, BM == 64 ? kAttrMma64 : kAttrMma128, smem);
   int extra = (p.last_tiles > 0 && p.nsplit_max > 0) ? p.B * p.last_tiles * p.nsplit_max : 0;
   dim3 grid((unsigned)(p.n_slots + extra), (unsigned)p.Hq);
   attn_mma_kernel<BM><<<grid, BM * 2, smem, s>>>(p);

@@ -165,7 +165,10 @@ attn_sm100_v3_kernel(const AttnParams p, const __grid_constant__ TmaMaps maps) {
   const int lane = threadIdx.x & 31;
 
   // ---- work item (uniform per CTA) -------------------------------------------
-  int n, r0, r1, lo0, cnt0, lo1, total, seq_start, h0, kvh, lrow;
+  // r0 / r1 / i are ABSOLUTE rows of the (context + chunk) sequence; q_row0 is the row of the
+  // query buffer that holds absolute row r0 (they differ by the sequence's context length).
+  int n, r0, r1, lo0, cnt0, lo1, total, seq_start, h0, kvh, lrow, seq = 0;
+  int q_row0, k_start;
   int pshift = 0;          // log2(P): query heads packed per group (kTail only)
   long long part = -1;     // split-KV partial index (kTail only)
   if constexpr (kTail) {
@@ -174,7 +177,8 @@ attn_sm100_v3_kernel(const AttnParams p, const __grid_constant__ TmaMaps maps) {
     const int TT = kBM >> pshift;
     int e = blockIdx.x;
     const int chunk = e % p.nsplit_max; e /= p.nsplit_max;
-    const int ql = e % p.last_tiles, seq = e / p.last_tiles;
+    const int ql = e % p.last_tiles;
+    seq = e / p.last_tiles;
     seq_start = p.cu[seq];
     n = p.cu[seq + 1] - seq_start;
     lrow = first_dense_row(n, p.last);
@@ -190,17 +194,22 @@ attn_sm100_v3_kernel(const AttnParams p, const __grid_constant__ TmaMaps maps) {
     lo1 = 0; total = cnt0;
     kvh = blockIdx.y; h0 = kvh * G;
     part = (long long)(seq * p.last_tiles + ql) * p.nsplit_max + chunk;
+    q_row0 = seq_start + r0; k_start = seq_start;
   } else {
     const SlotInfo slot = p.slots[p.n_slots - 1 - blockIdx.x];      // descending: longest first
     if (slot.seq < 0) return;
-    n = slot.n; r0 = slot.q_tile * kBM;
+    seq = slot.seq;
+    const SeqGeom gm = seq_geom(p, seq);
+    n = slot.n; r0 = gm.ctx + slot.q_tile * kBM;
     r1 = min(n, r0 + kBM) - 1;
+    lrow = first_dense_row(n, p.last);
+    if (p.tail_clip && p.mode == TMX_MODE_TRIANGLE && lrow < n) r1 = min(r1, lrow - 1);
     lo0 = slot.lo0; cnt0 = slot.hi0 - slot.lo0; lo1 = slot.lo1;
     total = cnt0 + (slot.hi1 - slot.lo1);
-    seq_start = p.cu[slot.seq];
+    seq_start = gm.q_start - gm.ctx;      // query-buffer row of absolute row 0 (may be negative)
+    q_row0 = gm.q_start + slot.q_tile * kBM; k_start = gm.k_start;
     h0 = 2 * blockIdx.y;
     kvh = h0 / (p.Hq / p.Hkv);
-    lrow = first_dense_row(n, p.last);
   }
   auto tile_of = [&](int it) { return it < cnt0 ? lo0 + it : lo1 + (it - cnt0); };
 
@@ -233,10 +242,10 @@ attn_sm100_v3_kernel(const AttnParams p, const __grid_constant__ TmaMaps maps) {
         for (int pnl = 0; pnl < 2; ++pnl)
           if constexpr (kTail)
             ptx::tma_load_3d(sQ + (g * 2 + pnl) * (kBM * 128), &maps.q, bar(bQFull), pnl * 64,
-                             h0 + (g << pshift), seq_start + r0);
+                             h0 + (g << pshift), q_row0);
           else
             ptx::tma_load_2d(sQ + (g * 2 + pnl) * (kBM * 128), &maps.q, bar(bQFull),
-                             (h0 + g) * kD + pnl * 64, seq_start + r0);
+                             (h0 + g) * kD + pnl * 64, q_row0);
       const int items = (kDbg == 2) ? 1 : 2 * total;     // item t: even = K(t/2), odd = V(t/2)
       int st = 0;
       // kTail streams K/V from HBM (no reuse across CTAs).  A CTA's own TMA boxes are 128-byte
@@ -249,7 +258,7 @@ attn_sm100_v3_kernel(const AttnParams p, const __grid_constant__ TmaMaps maps) {
       auto prefetch_tile = [&](int idx) {
         if (idx >= total) return;
         const int rbeg = kvh * pf_rows, rend = min(kBN, rbeg + pf_rows);
-        const long long tok0 = (long long)seq_start + (long long)tile_of(idx) * kBN;
+        const long long tok0 = (long long)k_start + (long long)tile_of(idx) * kBN;
         for (int r = rbeg; r < rend; ++r) {
           if (tok0 + r >= p.total_T) break;
           ptx::prefetch_l2(p.k + (tok0 + r) * p.kv_stride, (uint32_t)(p.Hkv * kD * 2));
@@ -258,15 +267,31 @@ attn_sm100_v3_kernel(const AttnParams p, const __grid_constant__ TmaMaps maps) {
       };
       if constexpr (kTail)
         for (int d = 0; d < kPfDist; ++d) prefetch_tile(d);
+      // Paged cache (chunked prefill / decode): a 128-key tile is gathered from its pages, one TMA box
+      // per page (page_size < 128) or one box inside a page (page_size >= 128).  Boxes past the last
+      // key re-read the last valid page (finite data; the scores there are masked anyway).
+      const int ps = p.page_size;
+      const int box_rows = (p.block_table != nullptr && ps < kBN) ? ps : kBN;
+      const int nbox = kBN / box_rows;
       for (int t = 0; t < items; ++t) {
         if constexpr (kTail) { if ((t & 1) == 0) prefetch_tile((t >> 1) + kPfDist); }
         if (t >= kStages) ptx::mbar_wait(bar(bEmpty + st), ((t / kStages) - 1) & 1);
         ptx::mbar_expect_tx(bar(bFull + st), kTileBytes);
-        const int row = seq_start + tile_of(t >> 1) * kBN;
+        const int key0 = tile_of(t >> 1) * kBN;
         const CUtensorMap* m = (t & 1) ? &maps.v : &maps.k;
-        for (int pnl = 0; pnl < 2; ++pnl)
-          ptx::tma_load_2d(sRing + st * kTileBytes + pnl * kPanelBytes, m, bar(bFull + st),
-                           kvh * kD + pnl * 64, row);
+        for (int bx = 0; bx < nbox; ++bx) {
+          int row;
+          if (p.block_table != nullptr) {
+            const int key = min(key0 + bx * box_rows, n - 1);
+            const int page = p.block_table[(long long)seq * p.bt_stride + key / ps];
+            row = page * ps + (ps > kBN ? key0 % ps : 0);
+          } else {
+            row = k_start + key0;
+          }
+          for (int pnl = 0; pnl < 2; ++pnl)
+            ptx::tma_load_2d(sRing + st * kTileBytes + pnl * kPanelBytes + bx * box_rows * 128, m,
+                             bar(bFull + st), kvh * kD + pnl * 64, row);
+        }
         if (++st == kStages) st = 0;
       }
     }
@@ -923,20 +948,24 @@ bool tail_tc_supported(int Hq, int Hkv, float scale_log2) {
   return (G == 2 || G == 4 || G == 8) && scale_log2 > 0.f;
 }
 
+// K/V descriptors: a contiguous [rows, Hkv * D] buffer (128-row boxes) or the paged cache viewed as
+// [num_blocks * page_size, Hkv * D] (one box per page when pages are shorter than a tile).
+static int kv_maps(TmaMaps* maps, const AttnParams& p) {
+  const int box = (p.block_table != nullptr && p.page_size < kBN) ? p.page_size : kBN;
+  int st = tma_map_2d(&maps->k, p.k, p.total_kv, (long long)p.Hkv * kD, p.kv_stride, box);
+  if (st == TMX_OK) st = tma_map_2d(&maps->v, p.v, p.total_kv, (long long)p.Hkv * kD, p.kv_stride, box);
+  return st;
+}
+
 // Dense tail rows of a triangle layer: split-KV workers on the tensor cores + merge.
 // p.tail_bm = tail_tc_block_m(), p.last_tiles / p.nsplit_max from the plan.
 int launch_attn_tail_tc(const AttnParams& p, cudaStream_t s) {
   const int G = p.Hq / p.Hkv, P = G / 2, TT = kBM / P;
-  auto kern = attn_sm100_v3_kernel<4, 0, true, false>;
-  static bool attr_set = false;
-  if (!attr_set) {
-    TMX_CUDA_TRY(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, kSmem));
-    attr_set = true;
-  }
+  auto kern = attn_sm100_v3_kernel<4, 0, true, 0>;
+  TMX_SET_SMEM_ATTR(kern, kAttrV3Tail, kSmem);
   TmaMaps maps;
   int st = tma_map_q3d(&maps.q, p.q, p.total_T, p.Hq, p.q_stride, P, TT);
-  if (st == TMX_OK) st = tma_map_2d(&maps.k, p.k, p.total_T, (long long)p.Hkv * kD, p.kv_stride, kBN);
-  if (st == TMX_OK) st = tma_map_2d(&maps.v, p.v, p.total_T, (long long)p.Hkv * kD, p.kv_stride, kBN);
+  if (st == TMX_OK) st = kv_maps(&maps, p);
   if (st != TMX_OK) return st;
   dim3 grid((unsigned)(p.B * p.last_tiles * p.nsplit_max), (unsigned)p.Hkv);
   kern<<<grid, kThreads, kSmem, s>>>(p, maps);
@@ -952,48 +981,47 @@ int launch_attn_tail_tc(const AttnParams& p, cudaStream_t s) {
 int launch_attn_sm100_v3(const AttnParams& p, int variant, cudaStream_t s) {
   if ((p.Hq / p.Hkv) % 2 != 0) return TMX_ERR_UNSUPPORTED;   // needs two query heads per KV head
   if (!(p.scale_log2 > 0.f)) return TMX_ERR_UNSUPPORTED;     // row max is taken on raw scores
-  // TMX_SM100_VARIANT bits 0-1: exponentials on the FMA pipe per 16 (0 = default 4, 1 = none, 2 = 6, 3 = 8;
-  // 4/16 measured best at 128K: 1121 vs 1088 TFLOP/s), bits 2-3: kDbg
-  const int emu = variant & 3, dbg = (variant >> 2) & 3;
   using Kern = void (*)(const AttnParams, const TmaMaps);
-  static const Kern table[4][4] = {
-      {attn_sm100_v3_kernel<4, 0, false, false>, attn_sm100_v3_kernel<0, 0, false, false>, attn_sm100_v3_kernel<6, 0, false, false>, attn_sm100_v3_kernel<8, 0, false, false>},
-      {attn_sm100_v3_kernel<0, 1, false, false>, attn_sm100_v3_kernel<0, 1, false, false>, attn_sm100_v3_kernel<0, 1, false, false>, attn_sm100_v3_kernel<0, 1, false, false>},
-      {attn_sm100_v3_kernel<0, 2, false, false>, attn_sm100_v3_kernel<4, 2, false, false>, attn_sm100_v3_kernel<6, 2, false, false>, attn_sm100_v3_kernel<8, 2, false, false>},
-      {attn_sm100_v3_kernel<0, 3, false, false>, attn_sm100_v3_kernel<4, 3, false, false>, attn_sm100_v3_kernel<6, 3, false, false>, attn_sm100_v3_kernel<8, 3, false, false>}};
-  Kern kern = table[dbg][emu];
-  // TMX_SM100_VARIANT bit 4: P stored in two halves with early PV issue (kSplitP).  Parity-green but
-  // measured SLOWER than the single store (1133 vs 1171 TFLOP/s at 32K, 1074 vs 1111 at 128K): the
-  // second store/fence/arrive and the lost TMEM-load overlap cost more than half a PV saves.
-  if (dbg == 0 && (variant & 16)) {
-    static const Kern split[4] = {attn_sm100_v3_kernel<4, 0, false, true>, attn_sm100_v3_kernel<0, 0, false, true>,
-                                  attn_sm100_v3_kernel<6, 0, false, true>, attn_sm100_v3_kernel<8, 0, false, true>};
-    kern = split[emu];
+  // Product kernel: the look-ahead variant with every exponential on MUFU (+1.2 % over the classic
+  // single-MMA-per-tile kernel at 128K, profiles/r01_sm100_v3_experiments.md section 7).
+  Kern kern = attn_sm100_v3_kernel<0, 0, false, 3>;
+  int slot = kAttrV3Dense;
+#ifdef TMX_DEV
+  // Developer build only (make DEV=1): timing / emulation variants selected by TMX_SM100_VARIANT.
+  // bits 0-1: exponentials on the FMA pipe per 16 (0 = 4, 1 = none, 2 = 6, 3 = 8); bits 2-3: kDbg
+  // (results are garbage); bit 4: kSplitP; bit 6: pipelined pass; 6+4: look-ahead; 6+5+4: polling issuer.
+  if (variant != 0) {
+    const int emu = variant & 3, dbg = (variant >> 2) & 3;
+    static const Kern table[4][4] = {
+        {attn_sm100_v3_kernel<4, 0, false, 0>, attn_sm100_v3_kernel<0, 0, false, 0>, attn_sm100_v3_kernel<6, 0, false, 0>, attn_sm100_v3_kernel<8, 0, false, 0>},
+        {attn_sm100_v3_kernel<0, 1, false, 0>, attn_sm100_v3_kernel<0, 1, false, 0>, attn_sm100_v3_kernel<0, 1, false, 0>, attn_sm100_v3_kernel<0, 1, false, 0>},
+        {attn_sm100_v3_kernel<0, 2, false, 0>, attn_sm100_v3_kernel<4, 2, false, 0>, attn_sm100_v3_kernel<6, 2, false, 0>, attn_sm100_v3_kernel<8, 2, false, 0>},
+        {attn_sm100_v3_kernel<0, 3, false, 0>, attn_sm100_v3_kernel<4, 3, false, 0>, attn_sm100_v3_kernel<6, 3, false, 0>, attn_sm100_v3_kernel<8, 3, false, 0>}};
+    kern = table[dbg][emu];
+    if (dbg == 0 && (variant & 16)) {
+      static const Kern split[4] = {attn_sm100_v3_kernel<4, 0, false, 1>, attn_sm100_v3_kernel<0, 0, false, 1>,
+                                    attn_sm100_v3_kernel<6, 0, false, 1>, attn_sm100_v3_kernel<8, 0, false, 1>};
+      kern = split[emu];
+    }
+    if (dbg == 0 && (variant & 64)) {
+      static const Kern pipe[4] = {attn_sm100_v3_kernel<4, 0, false, 2>, attn_sm100_v3_kernel<0, 0, false, 2>,
+                                   attn_sm100_v3_kernel<6, 0, false, 2>, attn_sm100_v3_kernel<8, 0, false, 2>};
+      static const Kern ahead[4] = {attn_sm100_v3_kernel<4, 0, false, 3>, attn_sm100_v3_kernel<0, 0, false, 3>,
+                                    attn_sm100_v3_kernel<6, 0, false, 3>, attn_sm100_v3_kernel<8, 0, false, 3>};
+      static const Kern poll[4] = {attn_sm100_v3_kernel<4, 0, false, 4>, attn_sm100_v3_kernel<0, 0, false, 4>,
+                                   attn_sm100_v3_kernel<6, 0, false, 4>, attn_sm100_v3_kernel<8, 0, false, 4>};
+      kern = (variant & 16) ? ((variant & 32) ? poll[emu] : ahead[emu]) : pipe[emu];
+    }
+    slot = -1;
   }
-  // TMX_SM100_VARIANT bit 6: softmax pass pipelined across its chunks (kSm == 2)
-  // bits 6 + 4 together (80): kSm == 3, pipelined pass + score MMA in two 64-key halves issued ahead
-  if (dbg == 0 && (variant & 64)) {
-    static const Kern pipe[4] = {attn_sm100_v3_kernel<4, 0, false, 2>, attn_sm100_v3_kernel<0, 0, false, 2>,
-                                 attn_sm100_v3_kernel<6, 0, false, 2>, attn_sm100_v3_kernel<8, 0, false, 2>};
-    static const Kern ahead[4] = {attn_sm100_v3_kernel<4, 0, false, 3>, attn_sm100_v3_kernel<0, 0, false, 3>,
-                                  attn_sm100_v3_kernel<6, 0, false, 3>, attn_sm100_v3_kernel<8, 0, false, 3>};
-    static const Kern poll[4] = {attn_sm100_v3_kernel<4, 0, false, 4>, attn_sm100_v3_kernel<0, 0, false, 4>,
-                                 attn_sm100_v3_kernel<6, 0, false, 4>, attn_sm100_v3_kernel<8, 0, false, 4>};
-    // bits 6 + 5 + 4 (112): kSm == 4, the look-ahead kernel with an event-driven MMA issuer
-    kern = (variant & 16) ? ((variant & 32) ? poll[emu] : ahead[emu]) : pipe[emu];
-  }
-  // Default (no switch set): the look-ahead kernel with every exponential on MUFU (== switch value 81),
-  // measured +1.2 % over the classic single-MMA-per-tile kernel at 128K (1123 vs 1110 TFLOP/s, four
-  // alternating pairs, profiles/r01_sm100_v3_experiments.md section 7).  TMX_SM100_CLASSIC=1 keeps the classic one.
-  if (variant == 0) {
-    static const bool classic = [] { const char* e = std::getenv("TMX_SM100_CLASSIC"); return e && std::atoi(e) != 0; }();
-    if (!classic) kern = attn_sm100_v3_kernel<0, 0, false, 3>;
-  }
-  TMX_CUDA_TRY(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, kSmem));
+#else
+  (void)variant;
+#endif
+  if (slot < 0) TMX_CUDA_TRY(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, kSmem));
+  else TMX_SET_SMEM_ATTR(kern, slot, kSmem);
   TmaMaps maps;
   int st = tma_map_2d(&maps.q, p.q, p.total_T, (long long)p.Hq * kD, p.q_stride, kBM);
-  if (st == TMX_OK) st = tma_map_2d(&maps.k, p.k, p.total_T, (long long)p.Hkv * kD, p.kv_stride, kBN);
-  if (st == TMX_OK) st = tma_map_2d(&maps.v, p.v, p.total_T, (long long)p.Hkv * kD, p.kv_stride, kBN);
+  if (st == TMX_OK) st = kv_maps(&maps, p);
   if (st != TMX_OK) return st;
   dim3 grid((unsigned)p.n_slots, (unsigned)(p.Hq / 2));
   kern<<<grid, kThreads, kSmem, s>>>(p, maps);

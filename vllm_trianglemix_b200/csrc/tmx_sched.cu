@@ -3,35 +3,40 @@
 // The idea of a per-row-block list of KV blocks is the one the reference tree's
 // csrc/attention/vertical_slash_index.cu uses for MInference; the TriangleMix
 // pattern (vertical sink + slash window + dense tail) needs at most two ranges.
-#include "tmx_sched.cuh"
+#include "tmx_attn.cuh"
 
 namespace tmx {
 
-__global__ void build_slots_kernel(SlotInfo* __restrict__ slots, const int* __restrict__ cu,
-                                   int bm, int bn, int si, int sl, int last, int mode) {
-  int b = blockIdx.y;
-  int start = cu[b], n = cu[b + 1] - start;
-  if (n <= 0) return;
-  int ntiles = ceil_div(n, bm);
-  int lrow = first_dense_row(n, last);
-  int base = start / bm + b;
+__global__ void build_slots_kernel(SlotInfo* __restrict__ slots, const AttnParams p, int bm, int bn) {
+  const int b = blockIdx.y;
+  const SeqGeom g = seq_geom(p, b);
+  if (g.nq <= 0 || g.ctx < 0) return;
+  const int ntiles = ceil_div(g.nq, bm);
+  const int lrow = first_dense_row(g.n, p.last);
+  const int base = g.q_start / bm + b;
   for (int q = blockIdx.x * blockDim.x + threadIdx.x; q < ntiles; q += gridDim.x * blockDim.x) {
-    int r0 = q * bm, r1 = min(n, r0 + bm) - 1;
-    TileRanges t = touched_tiles(r0, r1, n, bn, lrow, si, sl, mode);
+    // absolute rows of the tile inside the (context + chunk) sequence
+    const int r0 = g.ctx + q * bm;
+    int r1 = g.ctx + min(g.nq, (q + 1) * bm) - 1;
     SlotInfo s;
-    s.seq = b; s.q_tile = q; s.lo0 = t.lo0; s.hi0 = t.hi0; s.lo1 = t.lo1; s.hi1 = t.hi1;
-    s.nsplit = split_count(r0, r1, n, bn, lrow, last, mode, bm);
-    s.n = n;
+    s.seq = b; s.q_tile = q; s.n = g.n;
+    if (p.tail_clip && p.mode == TMX_MODE_TRIANGLE && lrow < g.n) {
+      // the dense tail rows [lrow, n) are served by the split-KV tail path
+      if (r0 >= lrow) { s.seq = -1; r1 = r0; }
+      else r1 = min(r1, lrow - 1);
+    }
+    const TileRanges t = touched_tiles(r0, r1, g.n, bn, lrow, p.si, p.sl, p.mode);
+    s.lo0 = t.lo0; s.hi0 = t.hi0; s.lo1 = t.lo1; s.hi1 = t.hi1;
+    s.nsplit = (g.ctx == 0 && !p.tail_clip) ? split_count(r0, r1, g.n, bn, lrow, p.last, p.mode, bm) : 0;
     slots[base + q] = s;
   }
 }
 
-int build_slots(SlotInfo* slots, int n_slots, const int* cu, int B, int max_seqlen, int bm, int bn,
-                int si, int sl, int last, int mode, cudaStream_t s) {
+int build_slots(SlotInfo* slots, int n_slots, const AttnParams& p, int bm, int bn, cudaStream_t s) {
   TMX_CUDA_TRY(cudaMemsetAsync(slots, 0xff, sizeof(SlotInfo) * (size_t)n_slots, s));
-  int tiles = ceil_div(max_seqlen > 0 ? max_seqlen : 1, bm);
-  dim3 grid((unsigned)min(ceil_div(tiles, 128), 1024), (unsigned)B);
-  build_slots_kernel<<<grid, 128, 0, s>>>(slots, cu, bm, bn, si, sl, last, mode);
+  int tiles = ceil_div(p.max_seqlen > 0 ? p.max_seqlen : 1, bm);
+  dim3 grid((unsigned)min(ceil_div(tiles, 128), 1024), (unsigned)p.B);
+  build_slots_kernel<<<grid, 128, 0, s>>>(slots, p, bm, bn);
   count_launch();
   TMX_CUDA_TRY(cudaGetLastError());
   return TMX_OK;

@@ -26,7 +26,8 @@ struct __align__(16) SlotInfo {
 
 constexpr int kSplitTiles = 32;       // KV tiles per split chunk
 constexpr int kSplitMinTiles = 64;    // split only tiles touching at least this many KV tiles
-constexpr int kSplitMaxLastRows = 512;
+constexpr int kSplitMaxLastRows = 512;    // mma.sync split path (fp32 partials grow with last x tiles)
+constexpr int kTailTcMaxRows = 8192;      // tcgen05 tail path: `last - 1` dense rows it will split
 
 __host__ __device__ __forceinline__ int ceil_div(int a, int b) { return (a + b - 1) / b; }
 
