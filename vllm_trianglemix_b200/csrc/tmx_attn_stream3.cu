@@ -1,0 +1,403 @@
+// Streaming part of a TriangleMix layer (sink columns + causal sliding window): the rows before
+// the dense tail, which at the reference's default parameters move 2.68 GB per 128K-token layer
+// for 0.08 TFLOP -- an HBM-bound pass.
+//
+// One M = 128 tile = TT = 128/G tokens x all G query heads of a KV head (packed row m = token
+// m / G, head m % G, loaded by ONE 3-D TMA box per 64-d panel), against the 16-key sink tile and
+// a window tile of nW = 16 * NWC keys: every byte of Q/K/V/O crosses HBM once.  One persistent
+// CTA per SM walks its tiles through a pipeline of 11 warps:
+//   warp 8      TMA producer: ring of stages (Q | K window | V window | K sink | V sink)
+//   warp 9      MMA issuer: S(t+1) is issued before PV(t); two TMEM sets (S/P columns + O columns)
+//   warps 0-3   softmax + epilogue of even tiles (TMEM set 0)
+//   warps 4-7   softmax + epilogue of odd tiles  (TMEM set 1)
+//   warp 10     TMA store: O tiles leave through the stage's dead Q buffer, one 3-D box per panel
+// Round-2 rewrite of the round-1 kernel (617 us at 128K = 4.3 TB/s).  ncu showed that kernel
+// issue-latency-bound (34 % issue slots, long-scoreboard stalls on TMEM loads):
+//   * its softmax walked the scores twice in rolled 16-column `tcgen05.ld -> wait -> math`
+//     steps (10 exposed round trips per tile); here the whole row (16 + nW <= 128 scores) is
+//     loaded once, with one wait, and both passes run from registers;
+//   * its MMA warp waited for a "TMEM set free" barrier before S(t+1), which serialised one
+//     group's PV behind the OTHER group's epilogue; the barrier is redundant (tcgen05 ops of one
+//     thread execute in issue order, and "P(t) ready" already implies that the group finished
+//     the epilogue of t-2), so it is gone;
+//   * the thread that issued the TMA store blocked its softmax warp in wait_group.read before
+//     releasing the stage; a dedicated store warp does that now.
+//
+// Replaces, for triangle layers, vllm/attention/ascend_trianglemix.py:86-106 of the reference.
+#include "tmx_attn.cuh"
+#include "tmx_sm100_ptx.cuh"
+#include "tmx_tma.cuh"
+
+namespace tmx {
+namespace {
+
+constexpr int kD = 128;
+constexpr int kSinkKeys = 16;
+constexpr int kMaxWin = 112;
+constexpr int kThreads3 = 352;
+constexpr int kQBytes = 2 * 128 * 128;           // [128 packed rows][128 d] bf16, two 64-d panels
+constexpr int kSinkBytes = kSinkKeys * 256;      // K or V sink tile, two panels
+constexpr int kStagesMax = 3;
+constexpr int kSmemBudget = 225 * 1024;
+constexpr uint32_t kColSink = 0, kColWin = 16, kColOut = 128, kColsPerSet = 256;
+
+// barriers: full[3] empty[3] staged[3] sfull[2] pready[2] ofull[2]
+constexpr int bFull = 0, bEmpty = 3, bStaged = 6, bSFull = 9, bPReady = 11, bOFull = 13, kNumBars3 = 15;
+
+struct Stream3Maps {
+  CUtensorMap q, kw, vw, ks, vs, o;
+};
+
+__device__ __forceinline__ uint32_t pack2s(float lo, float hi) {
+  __nv_bfloat162 v = __floats2bfloat162_rn(lo, hi);
+  return *reinterpret_cast<uint32_t*>(&v);
+}
+
+struct Tile {
+  int seq_start, r0, n, stream_end, kvh;
+  bool valid;
+};
+
+// Work item L (KV head fastest) -> tile; identical in every role.
+__device__ __forceinline__ Tile tile_at(const AttnParams& p, unsigned L, int TT) {
+  Tile t;
+  t.kvh = (int)(L % (unsigned)p.Hkv);
+  const SlotInfo s = p.slots[L / (unsigned)p.Hkv];
+  t.valid = s.seq >= 0;
+  t.n = s.n; t.r0 = s.q_tile * TT;
+  t.seq_start = t.valid ? p.cu[s.seq] : 0;
+  const int lrow = first_dense_row(t.n, p.last);
+  t.stream_end = lrow < t.n ? (lrow / p.tail_bm) * p.tail_bm : t.n;
+  t.valid = t.valid && t.r0 < t.stream_end;
+  return t;
+}
+
+template <int NWC>
+__global__ void __launch_bounds__(kThreads3, 1)
+attn_stream3_kernel(const AttnParams p, const __grid_constant__ Stream3Maps maps, const int G,
+                    const int n_stages, const unsigned n_items) {
+  constexpr int nW = NWC * 16;
+  constexpr int winBytes = nW * 256;                          // K or V window tile (two panels)
+  constexpr int winPanel = nW * 128;
+  constexpr uint32_t stageBytes = (uint32_t)(kQBytes + 2 * winBytes + 2 * kSinkBytes);
+  extern __shared__ uint8_t smem_raw[];
+  const uint32_t smem_base = (ptx::smem_u32(smem_raw) + 1023u) & ~1023u;
+  const uint32_t sBar = smem_base + (uint32_t)n_stages * stageBytes;
+  const uint32_t sTmemPtr = sBar + kNumBars3 * 8;
+  auto bar = [&](int i) { return sBar + 8u * (uint32_t)i; };
+  auto stage_base = [&](int st) { return smem_base + (uint32_t)st * stageBytes; };
+  const int warp = __shfl_sync(0xffffffffu, (int)(threadIdx.x >> 5), 0);
+  const int lane = threadIdx.x & 31;
+  const int TT = 128 / G;
+
+  if (warp == 8 && lane == 0) {
+    ptx::prefetch_tmap(&maps.q); ptx::prefetch_tmap(&maps.kw); ptx::prefetch_tmap(&maps.vw);
+    ptx::prefetch_tmap(&maps.ks); ptx::prefetch_tmap(&maps.vs); ptx::prefetch_tmap(&maps.o);
+    for (int s = 0; s < kStagesMax; ++s) {
+      ptx::mbar_init(bar(bFull + s), 1); ptx::mbar_init(bar(bEmpty + s), 1); ptx::mbar_init(bar(bStaged + s), 4);
+    }
+    for (int s = 0; s < 2; ++s) {
+      ptx::mbar_init(bar(bSFull + s), 1); ptx::mbar_init(bar(bPReady + s), 4); ptx::mbar_init(bar(bOFull + s), 1);
+    }
+    ptx::fence_barrier_init();
+  }
+  if (warp == 9) ptx::tmem_alloc(sTmemPtr, 512);
+  ptx::tc_fence_before();
+  __syncthreads();
+  ptx::tc_fence_after();
+  uint32_t tmem_base;
+  asm volatile("ld.shared.b32 %0, [%1];" : "=r"(tmem_base) : "r"(sTmemPtr));
+
+  if (warp == 8) {
+    // =========================== TMA producer ===========================
+    if (ptx::elect_one()) {
+      int t = 0;
+      for (unsigned L = blockIdx.x; L < n_items; L += gridDim.x) {
+        const Tile tl = tile_at(p, L, TT);
+        if (!tl.valid) continue;
+        const int st = t % n_stages;
+        if (t >= n_stages) ptx::mbar_wait(bar(bEmpty + st), ((t / n_stages) - 1) & 1);
+        const uint32_t sQ = stage_base(st), sKw = sQ + kQBytes, sVw = sKw + winBytes;
+        const uint32_t sKs = sVw + winBytes, sVs = sKs + kSinkBytes;
+        const uint32_t full = bar(bFull + st);
+        const int w0 = tl.r0 - p.sl, tok = tl.seq_start + tl.r0;
+        ptx::mbar_expect_tx(full, stageBytes);
+        for (int pnl = 0; pnl < 2; ++pnl) {
+          ptx::tma_load_3d(sQ + pnl * (128 * 128), &maps.q, full, pnl * 64, tl.kvh * G, tok);
+          ptx::tma_load_2d(sKs + pnl * (kSinkKeys * 128), &maps.ks, full, tl.kvh * kD + pnl * 64, tl.seq_start);
+          ptx::tma_load_2d(sKw + pnl * winPanel, &maps.kw, full, tl.kvh * kD + pnl * 64, tl.seq_start + w0);
+          ptx::tma_load_2d(sVs + pnl * (kSinkKeys * 128), &maps.vs, full, tl.kvh * kD + pnl * 64, tl.seq_start);
+          ptx::tma_load_2d(sVw + pnl * winPanel, &maps.vw, full, tl.kvh * kD + pnl * 64, tl.seq_start + w0);
+        }
+        ++t;
+      }
+    }
+    __syncwarp();
+  } else if (warp == 9) {
+    // =========================== MMA issuer ===========================
+    const uint32_t tb = __shfl_sync(0xffffffffu, tmem_base, 0);
+    constexpr uint32_t idS16 = ptx::instr_desc_bf16(128, kSinkKeys, false);
+    constexpr uint32_t idSW = ptx::instr_desc_bf16(128, nW, false);
+    constexpr uint32_t idO = ptx::instr_desc_bf16(128, 128, true);
+    // Scores of local tile t into TMEM set t & 1.  No "set free" wait: S(t) is issued after PV(t-2)
+    // by this same thread (tcgen05 ops execute in issue order), and PV(t-2) itself waited for P(t-2).
+    auto issue_s = [&](int t) {
+      const int st = t % n_stages, set = t & 1;
+      ptx::mbar_wait(bar(bFull + st), (t / n_stages) & 1);
+      ptx::tc_fence_after();
+      if (ptx::elect_one()) {
+        const uint32_t sQ = stage_base(st), sKw = sQ + kQBytes, sKs = sKw + 2 * winBytes;
+        const uint64_t dQ = ptx::smem_desc(sQ, 16, 1024);
+        const uint64_t dKs = ptx::smem_desc(sKs, 16, 1024), dKw = ptx::smem_desc(sKw, 16, 1024);
+        const uint32_t tc = tb + (uint32_t)set * kColsPerSet;
+#pragma unroll
+        for (int ks = 0; ks < 8; ++ks) {
+          const uint32_t qo = ((ks >> 2) * (128 * 128) + (ks & 3) * 32) >> 4;
+          ptx::mma_ss(tc + kColSink, dQ + qo, dKs + (((ks >> 2) * (kSinkKeys * 128) + (ks & 3) * 32) >> 4), idS16, ks > 0);
+          ptx::mma_ss(tc + kColWin, dQ + qo, dKw + (((ks >> 2) * winPanel + (ks & 3) * 32) >> 4), idSW, ks > 0);
+        }
+        ptx::mma_commit(bar(bSFull + set));
+      }
+      __syncwarp();
+    };
+    // how many valid tiles does this CTA own?  (same walk as the producer)
+    int ntiles = 0;
+    for (unsigned L = blockIdx.x; L < n_items; L += gridDim.x) ntiles += tile_at(p, L, TT).valid ? 1 : 0;
+    ntiles = __shfl_sync(0xffffffffu, ntiles, 0);
+    if (ntiles > 0) issue_s(0);
+    for (int t = 0; t < ntiles; ++t) {
+      if (t + 1 < ntiles) issue_s(t + 1);
+      const int st = t % n_stages, set = t & 1;
+      // P(t) stored => this group finished reading O(t-2) (its epilogue precedes its next softmax)
+      ptx::mbar_wait(bar(bPReady + set), (t >> 1) & 1);
+      ptx::tc_fence_after();
+      if (ptx::elect_one()) {
+        const uint32_t sVw = stage_base(st) + kQBytes + winBytes, sVs = sVw + winBytes + kSinkBytes;
+        const uint64_t dVs = ptx::smem_desc(sVs, kSinkKeys * 128, 1024), dVw = ptx::smem_desc(sVw, winPanel, 1024);
+        const uint32_t tc = tb + (uint32_t)set * kColsPerSet;
+        ptx::mma_ts(tc + kColOut, tc, dVs, idO, 0);          // sink keys: P columns [0,8)
+#pragma unroll
+        for (int ks = 0; ks < NWC; ++ks)
+          ptx::mma_ts(tc + kColOut, tc + 8 + (uint32_t)(ks * 8), dVw + (uint64_t)((ks * 2048) >> 4), idO, 1);
+        ptx::mma_commit(bar(bOFull + set));
+      }
+      __syncwarp();
+    }
+  } else if (warp == 10) {
+    // =========================== TMA store ===========================
+    // Tiles leave in order; a stage returns to the producer once its O tile has been READ out of
+    // shared memory (or at once, for the edge tiles the softmax warps stored row by row).
+    if (ptx::elect_one()) {
+      int t = 0;
+      for (unsigned L = blockIdx.x; L < n_items; L += gridDim.x) {
+        const Tile tl = tile_at(p, L, TT);
+        if (!tl.valid) continue;
+        const int st = t % n_stages;
+        ptx::mbar_wait(bar(bStaged + st), (t / n_stages) & 1);
+        if (tl.r0 + TT <= tl.stream_end) {
+          const uint32_t sO = stage_base(st);
+          ptx::tma_store_3d(&maps.o, sO, 0, tl.kvh * G, tl.seq_start + tl.r0);
+          ptx::tma_store_3d(&maps.o, sO + 128 * 128, 64, tl.kvh * G, tl.seq_start + tl.r0);
+          ptx::bulk_commit();
+          ptx::bulk_wait_read0();
+        }
+        ptx::mbar_arrive(bar(bEmpty + st));
+        ++t;
+      }
+      ptx::bulk_wait_all0();       // global writes complete before the CTA exits
+    }
+    __syncwarp();
+  } else {
+    // =========================== softmax + epilogue ===========================
+    // group = warp / 4 handles the local tiles t with (t & 1) == group, TMEM set = group.
+    const int grp = warp >> 2, w4 = warp & 3;
+    const int m = w4 * 32 + lane;                  // packed row: token m / G, head m % G
+    const uint32_t tl = tmem_base + ((uint32_t)(w4 * 32) << 16) + (uint32_t)grp * kColsPerSet;
+    const float sc = p.scale_log2;
+    int t = 0;
+    for (unsigned L = blockIdx.x; L < n_items; L += gridDim.x) {
+      const Tile tile = tile_at(p, L, TT);
+      if (!tile.valid) continue;
+      if ((t & 1) != grp) { ++t; continue; }
+      const int st = t % n_stages, use = t >> 1;   // `use`: how often this TMEM set was used before
+      const int i = tile.r0 + m / G;
+      const int head = tile.kvh * G + m % G;
+      const int w0 = tile.r0 - p.sl;
+      // attended columns: sink keys [0, shi] not already inside the window, window columns [clo, chi]
+      const int shi = min(min(p.si, i), i - p.sl - 1);
+      const int clo = max(0, i - p.sl) - w0, chi = i - w0;
+      const uint32_t sink_bits = bit_span32(0, shi) & 0xffffu;
+
+      ptx::mbar_wait(bar(bSFull + grp), use & 1);
+      ptx::tc_fence_after();
+      // the whole row at once: 16 sink scores + nW window scores, ONE wait
+      uint32_t xs[16];
+      uint32_t xw[NWC][16];
+      ptx::tmem_ld16(tl + kColSink, xs);
+#pragma unroll
+      for (int c = 0; c < NWC; ++c) ptx::tmem_ld16(tl + kColWin + (uint32_t)(c * 16), xw[c]);
+      ptx::tc_wait_ld();
+      float mx0 = -INFINITY, mx1 = -INFINITY;
+#pragma unroll
+      for (int e = 0; e < 16; e += 2) {
+        mx0 = ((sink_bits >> e) & 1u) ? fmaxf(mx0, __uint_as_float(xs[e])) : mx0;
+        mx1 = ((sink_bits >> (e + 1)) & 1u) ? fmaxf(mx1, __uint_as_float(xs[e + 1])) : mx1;
+      }
+#pragma unroll
+      for (int c = 0; c < NWC; ++c) {
+        const uint32_t bits = bit_span32(clo - c * 16, chi - c * 16);
+#pragma unroll
+        for (int e = 0; e < 16; e += 2) {
+          mx0 = ((bits >> e) & 1u) ? fmaxf(mx0, __uint_as_float(xw[c][e])) : mx0;
+          mx1 = ((bits >> (e + 1)) & 1u) ? fmaxf(mx1, __uint_as_float(xw[c][e + 1])) : mx1;
+        }
+      }
+      const float mx = fmaxf(mx0, mx1);
+      const float msc = (mx == -INFINITY) ? 0.f : mx * sc;
+      float l0 = 0.f, l1 = 0.f;
+      {
+        uint32_t pk[8];
+#pragma unroll
+        for (int e = 0; e < 16; e += 2) {
+          const float a = ((sink_bits >> e) & 1u) ? fast_exp2(fmaf(__uint_as_float(xs[e]), sc, -msc)) : 0.f;
+          const float b = ((sink_bits >> (e + 1)) & 1u) ? fast_exp2(fmaf(__uint_as_float(xs[e + 1]), sc, -msc)) : 0.f;
+          l0 += a; l1 += b;
+          pk[e / 2] = pack2s(a, b);
+        }
+        ptx::tmem_st8(tl, pk);                     // every score is in registers: P may overwrite S
+      }
+#pragma unroll
+      for (int c = 0; c < NWC; ++c) {
+        const uint32_t bits = bit_span32(clo - c * 16, chi - c * 16);
+        uint32_t pk[8];
+#pragma unroll
+        for (int e = 0; e < 16; e += 2) {
+          const float a = ((bits >> e) & 1u) ? fast_exp2(fmaf(__uint_as_float(xw[c][e]), sc, -msc)) : 0.f;
+          const float b = ((bits >> (e + 1)) & 1u) ? fast_exp2(fmaf(__uint_as_float(xw[c][e + 1]), sc, -msc)) : 0.f;
+          l0 += a; l1 += b;
+          pk[e / 2] = pack2s(a, b);
+        }
+        ptx::tmem_st8(tl + 8u + (uint32_t)(c * 8), pk);
+      }
+      ptx::tc_wait_st();
+      ptx::tc_fence_before();
+      __syncwarp();
+      if (lane == 0) ptx::mbar_arrive(bar(bPReady + grp));
+
+      const float l = l0 + l1;
+      const float inv = l > 0.f ? fast_rcp(l) : 0.f;
+      // whole tile inside the streamed rows -> TMA store through the stage's (dead) Q buffer
+      const bool tma_out = tile.r0 + TT <= tile.stream_end;
+      const uint32_t sO = stage_base(st);
+      __nv_bfloat16* orow = p.out + (long long)(tile.seq_start + i) * p.o_stride + head * kD;
+      if (p.lse != nullptr && i < tile.stream_end)
+        p.lse[(long long)head * p.total_T + tile.seq_start + i] = msc * 0.6931471805599453f + logf(l);
+      ptx::mbar_wait(bar(bOFull + grp), use & 1);
+      ptx::tc_fence_after();
+      auto emit = [&](int c, const uint32_t (&r)[32]) {
+#pragma unroll
+        for (int v4 = 0; v4 < 4; ++v4) {
+          uint4 o;
+          o.x = pack2s(__uint_as_float(r[v4 * 8 + 0]) * inv, __uint_as_float(r[v4 * 8 + 1]) * inv);
+          o.y = pack2s(__uint_as_float(r[v4 * 8 + 2]) * inv, __uint_as_float(r[v4 * 8 + 3]) * inv);
+          o.z = pack2s(__uint_as_float(r[v4 * 8 + 4]) * inv, __uint_as_float(r[v4 * 8 + 5]) * inv);
+          o.w = pack2s(__uint_as_float(r[v4 * 8 + 6]) * inv, __uint_as_float(r[v4 * 8 + 7]) * inv);
+          if (tma_out) {
+            // 128-byte-swizzled K-major panel layout (what the TMA box expects): 16-byte chunk ch of
+            // packed row m lives at m * 128 + ((ch ^ (m & 7)) << 4) inside its 64-d panel
+            const int d16 = c * 4 + v4;                     // 16-byte chunk of the 256-byte row
+            const uint32_t addr = sO + (uint32_t)((d16 >> 3) * (128 * 128) + m * 128 + (((d16 & 7) ^ (m & 7)) << 4));
+            asm volatile("st.shared.v4.b32 [%0], {%1, %2, %3, %4};" ::"r"(addr), "r"(o.x), "r"(o.y), "r"(o.z), "r"(o.w) : "memory");
+          } else if (i < tile.stream_end) {
+            *reinterpret_cast<uint4*>(orow + c * 32 + v4 * 8) = o;
+          }
+        }
+      };
+      {
+        // O (128 fp32 columns) in four 32-column loads, the next one in flight while one is converted
+        uint32_t ra[32], rb[32];
+        ptx::tmem_ld32(tl + kColOut, ra);
+        ptx::tc_wait_ld();
+        ptx::tmem_ld32(tl + kColOut + 32, rb);
+        emit(0, ra);
+        ptx::tc_wait_ld();
+        ptx::tmem_ld32(tl + kColOut + 64, ra);
+        emit(1, rb);
+        ptx::tc_wait_ld();
+        ptx::tmem_ld32(tl + kColOut + 96, rb);
+        emit(2, ra);
+        ptx::tc_wait_ld();
+        emit(3, rb);
+      }
+      ptx::tc_fence_before();
+      if (tma_out) ptx::fence_proxy_async_smem();           // st.shared -> visible to the TMA store
+      __syncwarp();
+      if (lane == 0) ptx::mbar_arrive(bar(bStaged + st));    // 4 warps: tile staged (or stored row by row)
+      ++t;
+    }
+  }
+
+  __syncthreads();
+  if (warp == 9) {
+    ptx::tc_fence_after();
+    ptx::tmem_dealloc(tmem_base, 512);
+  }
+}
+
+}  // namespace
+
+// Can the streaming kernel serve this triangle setting?  (G query heads per KV head packed
+// into M = 128, window of one CTA <= 112 keys, sink inside the first 16 keys.)
+bool stream_supported(int Hq, int Hkv, int si, int sl) {
+  if (Hkv <= 0 || Hq % Hkv != 0) return false;
+  const int G = Hq / Hkv;
+  if (G != 2 && G != 4 && G != 8) return false;
+  const int nW = (sl + 128 / G + 15) / 16 * 16;
+  return si >= 0 && si < kSinkKeys && sl >= 0 && nW <= kMaxWin;
+}
+int stream_block_m(int Hq, int Hkv) { return 128 / (Hq / Hkv); }
+
+template <int NWC>
+static int launch_stream3_t(const AttnParams& p, cudaStream_t s) {
+  const int G = p.Hq / p.Hkv, TT = 128 / G;
+  constexpr int nW = NWC * 16;
+  constexpr int stageBytes = kQBytes + 2 * nW * 256 + 2 * kSinkBytes;
+  int n_stages = (kSmemBudget - 2048) / stageBytes;
+  n_stages = n_stages > kStagesMax ? kStagesMax : n_stages;
+  if (n_stages < 2) return TMX_ERR_UNSUPPORTED;
+  const int smem = n_stages * stageBytes + kNumBars3 * 8 + 16 + 1024;
+  TMX_SET_SMEM_ATTR(attn_stream3_kernel<NWC>, kAttrStream3 + NWC, smem);
+  Stream3Maps maps;
+  int st = tma_map_q3d(&maps.q, p.q, p.total_T, p.Hq, p.q_stride, G, TT);
+  if (st == TMX_OK) st = tma_map_q3d(&maps.o, p.out, p.total_T, p.Hq, p.o_stride, G, TT);
+  if (st == TMX_OK) st = tma_map_2d(&maps.kw, p.k, p.total_T, (long long)p.Hkv * kD, p.kv_stride, nW);
+  if (st == TMX_OK) st = tma_map_2d(&maps.vw, p.v, p.total_T, (long long)p.Hkv * kD, p.kv_stride, nW);
+  if (st == TMX_OK) st = tma_map_2d(&maps.ks, p.k, p.total_T, (long long)p.Hkv * kD, p.kv_stride, kSinkKeys);
+  if (st == TMX_OK) st = tma_map_2d(&maps.vs, p.v, p.total_T, (long long)p.Hkv * kD, p.kv_stride, kSinkKeys);
+  if (st != TMX_OK) return st;
+  const unsigned n_items = (unsigned)p.n_slots * (unsigned)p.Hkv;
+  const unsigned sms = (unsigned)device_sm_count();
+  dim3 grid(n_items < sms ? n_items : sms);
+  attn_stream3_kernel<NWC><<<grid, kThreads3, smem, s>>>(p, maps, G, n_stages, n_items);
+  count_launch();
+  TMX_CUDA_TRY(cudaGetLastError());
+  return TMX_OK;
+}
+
+// p.slots: one slot per TT-token tile (build_slots with bm = TT); p.tail_bm: tile size of the
+// dense-tail path that owns the rows from its first tail tile on.
+int launch_attn_stream3(const AttnParams& p, cudaStream_t s) {
+  const int G = p.Hq / p.Hkv, TT = 128 / G;
+  const int nwc = (p.sl + TT + 15) / 16;
+  switch (nwc) {
+    case 1: case 2: return launch_stream3_t<2>(p, s);
+    case 3: return launch_stream3_t<3>(p, s);
+    case 4: return launch_stream3_t<4>(p, s);
+    case 5: return launch_stream3_t<5>(p, s);
+    case 6: return launch_stream3_t<6>(p, s);
+    case 7: return launch_stream3_t<7>(p, s);
+    default: return TMX_ERR_UNSUPPORTED;
+  }
+}
+
+}  // namespace tmx
