@@ -10,7 +10,10 @@
  * Conventions
  *   - every pointer is a DEVICE pointer unless its name ends in _host;
  *   - the caller owns all buffers (outputs and workspace); the library allocates
- *     nothing persistent except per-process cached TMA descriptors / attributes;
+ *     nothing persistent except cached TMA descriptors (per thread) and per-DEVICE
+ *     kernel attributes / SM count, so one process may drive several GPUs;
+ *   - the library reads no environment variable (developer timing variants exist
+ *     only in a `make DEV=1` build);
  *   - every call only ENQUEUES work on `stream` (a cudaStream_t) -- no host sync;
  *   - return value 0 = TMX_OK, otherwise a tmx_status (see tmx_strerror);
  *   - mask parameters: si = num_sink_tokens, sl = sliding_window_size,
@@ -145,6 +148,34 @@ int tmx_prefill_attn(void* out, const void* q, const void* k, const void* v,
                      int mode, const uint32_t* bitmask, int64_t bitmask_stride_words,
                      float* lse, void* workspace, size_t workspace_bytes, int kernel,
                      tmx_stream_t stream);
+
+/* ---- chunked prefill / prefix context / decode over the KV cache ----
+ * The same attention when the call's query rows are only the TAIL of each sequence: sequence b
+ * has seq_lens[b] keys (context + new tokens) and cu_seqlens_q[b+1] - cu_seqlens_q[b] query rows,
+ * which are rows seq_lens[b] - q_len .. seq_lens[b] - 1 of the (seq_lens[b] x seq_lens[b]) mask
+ * -- the triangle predicate's N is the full sequence length, as in the reference generator.
+ * Replaces the reference backend's context path, flash_attn_varlen_func(q, key_cache, value_cache,
+ * cu_seqlens_q, seqused_k, block_table, causal) (vllm/v1/attention/backends/flash_attn.py:518-548;
+ * metadata fields block_table / seq_lens :120-126).  K/V addressing, exactly one of:
+ *   block_table != NULL: k / v are the paged cache halves viewed as [num_blocks * page_size, Hkv*D]
+ *     rows (FlashAttention's NHD layout, flash_attn.py:78-87; kv_stride_t = elements per slot,
+ *     kv_rows = num_blocks * page_size); key j of sequence b sits in slot
+ *     block_table[b * block_table_stride + j / page_size] * page_size + j % page_size.
+ *     page_size: a multiple of 16 that divides 128, or a multiple of 128.  The tcgen05 kernel pulls
+ *     each 128-key tile with one TMA box per page.  Cache memory behind the listed pages must hold
+ *     finite values (vLLM zero-initialises it): masked keys still enter P x V with weight 0.
+ *   cu_seqlens_k != NULL: k / v are contiguous [sum seq_lens, Hkv, D] buffers (kv_rows rows).
+ * q_len == 1 rows are decode steps (served by the same kernels; correct, not decode-optimised).
+ * mode: TMX_MODE_DENSE_CAUSAL or TMX_MODE_TRIANGLE.  workspace: tmx_attn_workspace_bytes() of
+ * (B, total_Tq, max_query_len, ...) suffices.  lse (optional): float [Hq, total_Tq]. */
+int tmx_chunked_prefill_attn(void* out, const void* q, const int32_t* cu_seqlens_q,
+                             const int32_t* seq_lens, int B, int total_Tq, int max_query_len,
+                             int Hq, int Hkv, int D, int64_t q_stride_t, int64_t o_stride_t,
+                             const void* k, const void* v, int64_t kv_stride_t, int64_t kv_rows,
+                             const int32_t* cu_seqlens_k, const int32_t* block_table,
+                             int64_t block_table_stride, int page_size, float scale, int si,
+                             int sl, int last, int mode, float* lse, void* workspace,
+                             size_t workspace_bytes, int kernel, tmx_stream_t stream);
 
 /* ---- the step in front of attention -------------------
  * One HBM pass over q/k(/v): per-head RMSNorm of q and k (weight [D], fp32 variance),

@@ -189,6 +189,83 @@ def prefill_attn(q: torch.Tensor, k: torch.Tensor, v: torch.Tensor, cu_seqlens: 
     return (out, lse) if return_lse else out
 
 
+def chunked_prefill_attn(q: torch.Tensor, cu_seqlens_q: torch.Tensor, seq_lens: torch.Tensor, max_query_len: int,
+                         scale: float, si: int, sl: int, last: int, mode: int, *,
+                         key_cache: Optional[torch.Tensor] = None, value_cache: Optional[torch.Tensor] = None,
+                         block_table: Optional[torch.Tensor] = None,
+                         k: Optional[torch.Tensor] = None, v: Optional[torch.Tensor] = None,
+                         cu_seqlens_k: Optional[torch.Tensor] = None,
+                         out: Optional[torch.Tensor] = None, return_lse: bool = False, kernel: str = "auto"):
+    """Attention of the LAST q_len rows of each sequence over all seq_lens[b] keys (chunked prefill,
+    prefix-cache hits, decode): the context path of the reference backend,
+    flash_attn_varlen_func(q, key_cache, value_cache, cu_seqlens_q, seqused_k, block_table)
+    (vllm/v1/attention/backends/flash_attn.py:518-548).
+
+    q [Tq, Hq, D] bf16; seq_lens int32 [B] (context + new tokens).  K/V either from the paged cache
+    (key_cache / value_cache [num_blocks, block_size, Hkv, D] NHD views + block_table int32
+    [B, max_blocks]) or contiguous (k / v [sum seq_lens, Hkv, D] + cu_seqlens_k)."""
+    device = _require_cuda(q.device)
+    lib = _lib.load()
+    if q.dtype != torch.bfloat16 or q.dim() != 3:
+        raise _lib.TmxError("chunked_prefill_attn needs bf16 q [Tq, Hq, D], got %s %r" % (q.dtype, tuple(q.shape)))
+    t, hq, d = q.shape
+    if not (q.stride(2) == 1 and q.stride(1) == d):
+        q = q.contiguous()
+    if out is None:
+        out = torch.empty((t, hq, d), dtype=torch.bfloat16, device=device)
+    elif out.dtype != torch.bfloat16 or out.stride(2) != 1 or out.stride(1) != d:
+        raise _lib.TmxError("out must be bf16 [Tq,Hq,D] with contiguous heads")
+
+    def i32(x):
+        return x if (x.dtype == torch.int32 and x.is_contiguous()) else x.to(torch.int32).contiguous()
+
+    cu_q, lens = i32(cu_seqlens_q), i32(seq_lens)
+    b = lens.numel()
+    if cu_q.numel() != b + 1:
+        raise _lib.TmxError("cu_seqlens_q has %d entries for %d sequences" % (cu_q.numel(), b))
+    if block_table is not None:
+        if key_cache is None or value_cache is None:
+            raise _lib.TmxError("block_table needs key_cache and value_cache")
+        blk, tok, head, page = _cache_strides(key_cache, value_cache)
+        hkv = key_cache.shape[2]
+        if head != d or blk != page * tok:
+            raise _lib.TmxError("the paged read path needs the NHD cache layout [num_blocks, block_size, Hkv, D] "
+                                "(FlashAttention's, flash_attn.py:78-87); got strides %r" % (key_cache.stride(),))
+        bt = block_table if (block_table.dtype == torch.int32 and block_table.stride(-1) == 1) \
+            else block_table.to(torch.int32).contiguous()
+        if bt.dim() != 2 or bt.shape[0] < b:
+            raise _lib.TmxError("block_table must be int32 [B, max_blocks]")
+        kptr, vptr, kv_stride, kv_rows = key_cache.data_ptr(), value_cache.data_ptr(), tok, key_cache.shape[0] * page
+        cuk_ptr, bt_ptr, bt_stride = None, bt.data_ptr(), bt.stride(0)
+    else:
+        if k is None or v is None or cu_seqlens_k is None:
+            raise _lib.TmxError("pass either (key_cache, value_cache, block_table) or (k, v, cu_seqlens_k)")
+        if k.dtype != torch.bfloat16 or v.dtype != torch.bfloat16 or k.dim() != 3 or v.shape != k.shape:
+            raise _lib.TmxError("k / v must be bf16 [sum seq_lens, Hkv, D]")
+
+        def tok_major(x):
+            return x if (x.stride(2) == 1 and x.stride(1) == x.shape[2]) else x.contiguous()
+        k, v = tok_major(k), tok_major(v)
+        if k.stride(0) != v.stride(0):
+            k, v = k.contiguous(), v.contiguous()
+        hkv, page = k.shape[1], 0
+        cu_k = i32(cu_seqlens_k)
+        kptr, vptr, kv_stride, kv_rows = k.data_ptr(), v.data_ptr(), k.stride(0), k.shape[0]
+        cuk_ptr, bt_ptr, bt_stride = cu_k.data_ptr(), None, 0
+    kcode = KERNELS[kernel]
+    lse = torch.empty((hq, t), dtype=torch.float32, device=device) if return_lse else None
+    with torch.cuda.device(device):
+        need = lib.tmx_attn_workspace_bytes(b, t, max_query_len, hq, hkv, d, si, sl, last, int(mode), kcode)
+        ws = _workspace(device, need)
+        st = lib.tmx_chunked_prefill_attn(
+            out.data_ptr(), q.data_ptr(), cu_q.data_ptr(), lens.data_ptr(), b, t, max_query_len, hq, hkv, d,
+            q.stride(0), out.stride(0), kptr, vptr, kv_stride, kv_rows, cuk_ptr, bt_ptr, bt_stride, page,
+            float(scale), si, sl, last, int(mode), None if lse is None else lse.data_ptr(),
+            ws.data_ptr(), ws.numel(), kcode, _stream(device))
+    _lib.check(st, "tmx_chunked_prefill_attn")
+    return (out, lse) if return_lse else out
+
+
 def _cache_strides(key_cache: torch.Tensor, value_cache: torch.Tensor):
     """(block, token, head) element strides of a [num_blocks, block_size, Hkv, D] cache view
     (NHD as FlashAttention allocates it, flash_attn.py:78-87, or an HND-permuted view)."""
