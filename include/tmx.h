@@ -100,8 +100,10 @@ int tmx_mask_rewrite_neg_inf(void* out, const void* in, int dtype, int64_t numel
 
 /* Arbitrary additive N x N mask (values 0 / -inf, as a caller may pass in
  * `attn_mask`, vllm/attention/ascend_trianglemix.py:57,84,97) -> packed bitmask
- * (warp ballot).  *bad_count (device int32, may be null) receives the number of
- * elements that are neither 0 nor -inf. */
+ * (warp ballot).  0 = attend; -inf or any value <= -1e4 = masked (covers the -1e6
+ * that optimize_mask_for_npu writes, :135-139: its softmax weight is exactly 0 in
+ * fp32 next to any attended key).  *bad_count (device int32, may be null) receives
+ * the number of elements that are neither. */
 int tmx_mask_bits_from_additive(uint32_t* out, int64_t row_stride_words,
                                 const void* in, int dtype, int64_t ld, int N,
                                 int32_t* bad_count, tmx_stream_t stream);

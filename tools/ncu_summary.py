@@ -1,6 +1,27 @@
 """Summarise an .ncu-rep (raw + source pages) here on the CPU box: key metrics and top stall sites."""
-import csv, re, subprocess, sys
+import collections, csv, re, subprocess, sys
 
+
+def launches(path):
+    """Per-kernel launch counts / average duration from an `ncu --metrics gpu__time_duration.sum --csv` log."""
+    rows = [r for r in csv.reader(open(path, errors="replace")) if len(r) > 10]
+    hdr = rows[0]
+    ki, vi, gi = hdr.index("Kernel Name"), hdr.index("Metric Value"), hdr.index("Grid Size")
+    agg = collections.OrderedDict()
+    for r in rows[1:]:
+        try:
+            agg.setdefault((re.sub(r"\(.*", "", r[ki])[:70], r[gi]), []).append(float(r[vi].replace(",", "")))
+        except ValueError:
+            pass
+    total = sum(sum(v) for v in agg.values())
+    for (name, grid), v in agg.items():
+        print("%-70s grid %-16s n=%-4d avg %9.1f us  share %5.1f %%" % (name, grid, len(v), sum(v) / len(v) / 1e3,
+                                                                      100 * sum(v) / max(total, 1)))
+
+
+if sys.argv[1] == "--launches":
+    launches(sys.argv[2])
+    sys.exit(0)
 rep = sys.argv[1]
 topn = int(sys.argv[2]) if len(sys.argv) > 2 else 25
 raw = subprocess.run(["ncu", "-i", rep, "--page", "raw", "--csv"], capture_output=True, text=True).stdout

@@ -83,9 +83,11 @@ class AscendTriangleMixAttention(nn.Module):
             mode, si, sl, last = layer
         if attn_mask is not None:
             spec = getattr(attn_mask, "_tmx_mask_spec", None)
+            if spec is not None and spec[5] != attn_mask._version:
+                spec = None                            # edited in place since the generator made it
             if spec is not None and spec[0] == s and (
                     layer is None or (spec[4], spec[1], spec[2], spec[3]) == tuple(layer)):
-                _, si, sl, last, mode = spec           # a mask made by our generator: analytic path
+                _, si, sl, last, mode, _ = spec        # a mask made by our generator: analytic path
             else:
                 bitmask = self._bits_of_user_mask(attn_mask, s)
                 if layer is not None:                  # attn_mask + tri_mask  ==  AND of the bit sets
@@ -107,8 +109,8 @@ class AscendTriangleMixAttention(nn.Module):
             raise TmxError("attn_mask dtype must be float32/bfloat16/float16, got %s" % attn_mask.dtype)
         bits, bad = ops.bits_from_additive(attn_mask)
         if int(bad.item()) != 0:
-            raise TmxError("attn_mask holds %d values other than 0 / -inf; only 0/-inf additive masks "
-                           "are supported (no eager fallback)" % int(bad.item()))
+            raise TmxError("attn_mask holds %d values other than 0 and -inf (or <= -1e4); only such additive "
+                           "masks are supported (no eager fallback)" % int(bad.item()))
         return bits
 
 

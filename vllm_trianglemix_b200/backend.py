@@ -11,10 +11,11 @@ ChunkedLocalAttention / EncoderOnlyAttention install theirs:
 * in-place ``output`` contract          vllm/v1/attention/backends/flash_attn.py:449-458,549
 
 The classes are duck-typed (no ``import vllm``: the vllm wheel in this image is an
-unrelated upstream release).  Prefill only: K/V of the call are the whole
-context, as in ``_forward_encoder_attention`` (flash_attn.py:578-633); a ``kv_cache``
-is written (new K/V rows at ``attn_metadata.slot_mapping``, flash_attn.py:483-507) but
-never read.  TriangleMix parameters and ``layer_idx`` travel as extra impl kwargs,
+unrelated upstream release).  The new K/V rows are written to the paged ``kv_cache`` at
+``attn_metadata.slot_mapping`` (flash_attn.py:483-507).  A whole-sequence prefill attends the
+call's own K/V (as ``_forward_encoder_attention`` does, flash_attn.py:578-633); a batch that
+carries context keys (chunked prefill, prefix-cache hit, decode: ``seq_lens`` > query lengths)
+reads all keys back from the cache through ``block_table`` (flash_attn.py:518-548).  TriangleMix parameters and ``layer_idx`` travel as extra impl kwargs,
 the way ``dual_chunk_attention_config`` + ``layer_idx`` do in the reference's
 vllm/model_executor/models/qwen3.py:150-153.
 """
@@ -37,40 +38,69 @@ class TriangleMixMetadata:
     max_query_len: int
     query_start_loc: torch.Tensor          # int32 [B+1] on the device
     max_seq_len: int
-    seq_lens: Optional[torch.Tensor] = None
+    seq_lens: Optional[torch.Tensor] = None          # int32 [B]: context + new tokens (flash_attn.py:124)
     causal: bool = True
     query_start_loc_cpu: Optional[torch.Tensor] = None
     slot_mapping: Optional[torch.Tensor] = None   # int64 [num_actual_tokens], flash_attn.py:127
+    block_table: Optional[torch.Tensor] = None    # int32 [B, max_blocks], flash_attn.py:125
+    seq_lens_cpu: Optional[torch.Tensor] = None
+    # True when some sequence brings context keys (chunked prefill, prefix-cache hit, decode):
+    # the keys then come from the paged cache.  None = unknown (decided from the CPU copies).
+    has_context: Optional[bool] = None
+
+    def context_present(self) -> bool:
+        if self.has_context is not None:
+            return bool(self.has_context)
+        if self.max_seq_len != self.max_query_len:
+            return True
+        if self.seq_lens_cpu is not None and self.query_start_loc_cpu is not None:
+            qlen = self.query_start_loc_cpu[1:] - self.query_start_loc_cpu[:-1]
+            return bool((self.seq_lens_cpu[:qlen.numel()].to(qlen.dtype) != qlen).any())
+        return False
 
 
 class TriangleMixMetadataBuilder:
     """Builds TriangleMixMetadata from the fields of CommonAttentionMetadata
-    (vllm/v1/attention/backends/utils.py:45-84)."""
+    (vllm/v1/attention/backends/utils.py:45-84), the way FlashAttentionMetadataBuilder.build does
+    (vllm/v1/attention/backends/flash_attn.py:208-330)."""
 
     def __init__(self, kv_cache_spec=None, layer_names=None, vllm_config=None, device=None):
+        self.kv_cache_spec = kv_cache_spec
+        self.layer_names = layer_names
+        self.vllm_config = vllm_config
         self.device = device
 
     def build(self, common_prefix_len: int = 0, common_attn_metadata=None, fast_build: bool = False):
         m = common_attn_metadata
+        computed = getattr(m, "num_computed_tokens_cpu", None)
+        has_ctx = None if computed is None else bool((computed[:int(getattr(m, "num_reqs", computed.numel()))] > 0).any())
         return TriangleMixMetadata(
             num_actual_tokens=int(m.num_actual_tokens), max_query_len=int(m.max_query_len),
             query_start_loc=m.query_start_loc, max_seq_len=int(getattr(m, "max_seq_len", m.max_query_len)),
             seq_lens=getattr(m, "seq_lens", None), causal=getattr(m, "causal", True),
             query_start_loc_cpu=getattr(m, "query_start_loc_cpu", None),
-            slot_mapping=getattr(m, "slot_mapping", None))
+            slot_mapping=getattr(m, "slot_mapping", None),
+            block_table=getattr(m, "block_table_tensor", getattr(m, "block_table", None)),
+            seq_lens_cpu=getattr(m, "seq_lens_cpu", None), has_context=has_ctx)
 
     @staticmethod
-    def from_seq_lens(seq_lens: List[int], device) -> TriangleMixMetadata:
-        """Convenience for tests / benchmarks: prefill of len(seq_lens) whole sequences."""
+    def from_seq_lens(seq_lens: List[int], device, query_lens: Optional[List[int]] = None,
+                      block_table: Optional[torch.Tensor] = None,
+                      slot_mapping: Optional[torch.Tensor] = None) -> TriangleMixMetadata:
+        """Convenience for tests / benchmarks: a batch whose sequence b has seq_lens[b] keys, the last
+        query_lens[b] of them being this call's query rows (default: all of them = whole-sequence prefill)."""
+        qlens = list(seq_lens) if query_lens is None else list(query_lens)
         cu = [0]
-        for n in seq_lens:
+        for n in qlens:
             cu.append(cu[-1] + int(n))
         cu_cpu = torch.tensor(cu, dtype=torch.int32)
+        lens_cpu = torch.tensor(list(seq_lens), dtype=torch.int32)
         return TriangleMixMetadata(
-            num_actual_tokens=cu[-1], max_query_len=max(seq_lens) if seq_lens else 0,
+            num_actual_tokens=cu[-1], max_query_len=max(qlens) if qlens else 0,
             query_start_loc=cu_cpu.to(device), max_seq_len=max(seq_lens) if seq_lens else 0,
-            seq_lens=torch.tensor(list(seq_lens), dtype=torch.int32, device=device),
-            causal=True, query_start_loc_cpu=cu_cpu)
+            seq_lens=lens_cpu.to(device), causal=True, query_start_loc_cpu=cu_cpu,
+            slot_mapping=slot_mapping, block_table=block_table, seq_lens_cpu=lens_cpu,
+            has_context=any(int(a) != int(b) for a, b in zip(seq_lens, qlens)))
 
 
 class TriangleMixImpl:
@@ -154,10 +184,70 @@ class TriangleMixImpl:
             # store the new K/V rows in the paged cache (flash_attn.py:483-507)
             key_cache, value_cache = kv_cache.unbind(0)
             ops.reshape_and_cache_flash(k, v, key_cache, value_cache, slot_mapping, self.kv_cache_dtype)
+        return self.attend(q, k, v, kv_cache, attn_metadata, out, output)
+
+    def attend(self, q, k, v, kv_cache, attn_metadata: TriangleMixMetadata, out, output):
+        """The attention itself, after the new K/V rows are in the cache (callers that fuse the
+        cache write into an earlier kernel -- Qwen3TriangleMixAttention -- enter here).
+        q/k/v/out: [T, H, D] views of the actual tokens; returns `output`."""
         mode, si, sl, last = self.mask_mode()
-        ops.prefill_attn(q, k, v, attn_metadata.query_start_loc, attn_metadata.max_query_len, self.scale,
-                         si, sl, last, mode, out=out, kernel=self.kernel)
+        if attn_metadata.context_present():
+            # Chunked prefill / prefix-cache hit / decode: the keys are the cache's, through the block
+            # table (flash_attn.py:518-548).  Query rows are the LAST rows of each sequence, so the
+            # triangle predicate sees the full sequence length.
+            if kv_cache is None or kv_cache.numel() == 0 or attn_metadata.block_table is None \
+                    or attn_metadata.seq_lens is None:
+                raise NotImplementedError(
+                    "this batch carries context keys (seq_lens != query lengths: chunked prefill, a prefix-cache "
+                    "hit or a decode step) but no kv_cache / block_table / seq_lens to read them from")
+            key_cache, value_cache = kv_cache.unbind(0)
+            ops.chunked_prefill_attn(q, attn_metadata.query_start_loc, attn_metadata.seq_lens,
+                                     attn_metadata.max_query_len, self.scale, si, sl, last,
+                                     self._context_mode(mode, attn_metadata), key_cache=key_cache,
+                                     value_cache=value_cache, block_table=attn_metadata.block_table, out=out,
+                                     kernel=self.kernel)
+            return output
+        self._whole_sequence_prefill(q, k, v, out, attn_metadata, mode, si, sl, last)
         return output
+
+    # The reference helper hands out no mask at seq_len <= 2048 (trianglemix_attention.py:330-332): such a
+    # sequence runs on the stock causal backend even in a triangle layer.
+    SHORT_SEQ_DENSE = 2048
+
+    def _context_mode(self, mode: int, md: TriangleMixMetadata) -> int:
+        if mode != ops.TRIANGLE:
+            return mode
+        if md.max_seq_len <= self.SHORT_SEQ_DENSE:
+            return ops.DENSE_CAUSAL
+        if md.seq_lens_cpu is not None and bool((md.seq_lens_cpu <= self.SHORT_SEQ_DENSE).any()):
+            raise NotImplementedError("a chunked batch mixing sequences <= 2048 (dense by the reference's threshold) "
+                                      "and > 2048 tokens in a triangle layer: schedule them in separate steps")
+        return mode
+
+    def _whole_sequence_prefill(self, q, k, v, out, md: TriangleMixMetadata, mode, si, sl, last) -> None:
+        cu, cu_cpu = md.query_start_loc, md.query_start_loc_cpu
+        if mode != ops.TRIANGLE or cu_cpu is None:
+            if mode == ops.TRIANGLE and md.max_query_len <= self.SHORT_SEQ_DENSE:
+                mode = ops.DENSE_CAUSAL
+            ops.prefill_attn(q, k, v, cu, md.max_query_len, self.scale, si, sl, last, mode, out=out,
+                             kernel=self.kernel)
+            return
+        # triangle layer: sequences <= 2048 tokens are dense-causal, longer ones triangle.  Runs of
+        # consecutive sequences of one class are contiguous token ranges -> one kernel call per run.
+        lens = (cu_cpu[1:] - cu_cpu[:-1]).tolist()
+        starts = cu_cpu.tolist()
+        b0 = 0
+        while b0 < len(lens):
+            short = lens[b0] <= self.SHORT_SEQ_DENSE
+            b1 = b0
+            while b1 < len(lens) and (lens[b1] <= self.SHORT_SEQ_DENSE) == short:
+                b1 += 1
+            t0, t1 = starts[b0], starts[b1]
+            if t1 > t0:
+                sub_cu = cu if (b0 == 0 and b1 == len(lens)) else (cu[b0:b1 + 1] - cu[b0]).contiguous()
+                ops.prefill_attn(q[t0:t1], k[t0:t1], v[t0:t1], sub_cu, max(lens[b0:b1]), self.scale, si, sl, last,
+                                 ops.DENSE_CAUSAL if short else ops.TRIANGLE, out=out[t0:t1], kernel=self.kernel)
+            b0 = b1
 
 
 class TriangleMixBackend:

@@ -134,7 +134,9 @@ bits_from_additive_kernel(uint32_t* __restrict__ out, long long row_stride_words
       if (wbase + w < row_stride_words && c < n) {
         float x = (float)src[c];
         on = (x == 0.0f);
-        bad += (!on && !is_neg_inf(x));
+        // masked: -inf, or any value <= -1e4 (e.g. the -1e6 that optimize_mask_for_npu writes,
+        // reference ascend_trianglemix.py:135-139): exp(score + x - rowmax) is exactly 0 in fp32
+        bad += (!on && !(x <= -1.0e4f));
       }
       uint32_t word = __ballot_sync(0xffffffffu, on);
       if (w == lane) mine = word;

@@ -88,5 +88,10 @@ class Qwen3TriangleMixAttention(nn.Module):
             cache_args = dict(v=v, key_cache=key_cache, value_cache=value_cache, slot_mapping=slot_mapping)
         q, k = ops.qk_norm_rope(positions, q, k, self.q_norm_weight, self.k_norm_weight, self.cos_sin_cache,
                                 self.rms_norm_eps, self.head_dim, inplace=True, **cache_args)
-        # the cache rows are already written: hand the impl no cache so it does not write them again
-        return self.impl.forward(None, q, k, v, None if fused_cache else kv_cache, attn_metadata, output=output)
+        if not fused_cache or attn_metadata is None:
+            return self.impl.forward(None, q, k, v, kv_cache, attn_metadata, output=output)
+        # the cache rows are already written by the fused kernel: enter the impl after its cache write
+        t, impl = attn_metadata.num_actual_tokens, self.impl
+        return impl.attend(q[:t].view(t, impl.num_heads, impl.head_size), k[:t].view(t, impl.num_kv_heads, impl.head_size),
+                           v[:t].view(t, impl.num_kv_heads, impl.head_size), kv_cache, attn_metadata,
+                           output[:t].view(t, impl.num_heads, impl.head_size), output)

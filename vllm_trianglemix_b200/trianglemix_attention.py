@@ -77,7 +77,9 @@ class TriangleMixMaskGenerator(nn.Module):
                                  ops.TRIANGLE if use_triangle else ops.DENSE_CAUSAL, device, dtype)
         # tag the tensor so the attention op can recognise a generator-made mask and use the
         # block index instead of reading N x N values back
-        mask._tmx_mask_spec = (seq_len, si, sl, last, ops.TRIANGLE if use_triangle else ops.DENSE_CAUSAL)
+        # (the tag carries the tensor's version counter: an in-place edit by the caller voids it)
+        mask._tmx_mask_spec = (seq_len, si, sl, last, ops.TRIANGLE if use_triangle else ops.DENSE_CAUSAL,
+                               mask._version)
         self._mask_cache[cache_key] = mask
         return mask
 
