@@ -150,8 +150,15 @@ Plan make_plan(int B, int total_T, int max_seqlen, int Hq, int Hkv, int si, int 
   return pl;
 }
 
+#ifdef TMX_DEV
+long long* g_trace = nullptr;
+#endif
+
 // Shared by both entry points once the arguments are validated and AttnParams is filled.
 int run_plan(const Plan& pl, AttnParams& p, uint8_t* ws, cudaStream_t s) {
+#ifdef TMX_DEV
+  p.trace = g_trace;
+#endif
   p.slots = reinterpret_cast<SlotInfo*>(ws + pl.off_slots);
   p.part_o = reinterpret_cast<float*>(ws + pl.off_part_o);
   p.part_ml = reinterpret_cast<float2*>(ws + pl.off_part_ml);
@@ -204,6 +211,12 @@ extern "C" const char* tmx_last_cuda_error(void) {
 
 extern "C" int tmx_version(void) { return 100; }
 extern "C" int tmx_last_launch_count(void) { return g_launches; }
+
+#ifdef TMX_DEV
+// Developer library only: device buffer of 4 x 96 x 12 int64 that the streaming kernel fills with
+// clock64 stamps of its pipeline events (tools/stream_trace.py); null switches the trace off.
+extern "C" void tmx_dev_set_trace(long long* buf) { g_trace = buf; }
+#endif
 
 extern "C" size_t tmx_attn_workspace_bytes(int B, int total_T, int max_seqlen, int Hq, int Hkv,
                                            int D, int si, int sl, int last, int mode, int kernel) {

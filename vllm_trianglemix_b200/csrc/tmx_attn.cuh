@@ -33,6 +33,7 @@ struct AttnParams {
   int tail_bm;                // stream kernel: query-tile size of the dense-tail path
   int tail_clip;              // block-index kernels: rows >= the first dense row belong to the tail path
   float scale_log2;           // scale * log2(e)
+  long long* trace;           // developer build only (tmx_dev_set_trace): clock64 timeline buffer, else null
 };
 
 // Per-sequence geometry, identical in every kernel.

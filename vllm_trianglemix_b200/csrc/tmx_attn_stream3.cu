@@ -5,9 +5,11 @@
 // One M = 128 tile = TT = 128/G tokens x all G query heads of a KV head (packed row m = token
 // m / G, head m % G, loaded by ONE 3-D TMA box per 64-d panel), against the 16-key sink tile and
 // a window tile of nW = 16 * NWC keys: every byte of Q/K/V/O crosses HBM once.  One persistent
-// CTA per SM walks its tiles through a pipeline of 11 warps:
+// CTA per SM walks its tiles through a pipeline of 12 warps:
 //   warp 8      TMA producer: ring of stages (Q | K window | V window | K sink | V sink)
-//   warp 9      MMA issuer: S(t+1) is issued before PV(t); two TMEM sets (S/P columns + O columns)
+//   warp 9      score issuer: S(t) = Q K^T as soon as tile t has landed; two TMEM sets (S | P | O columns)
+//   warp 11     PV issuer: O(t) = P V as soon as P(t) is stored (an in-order single issuer made PV(t)
+//               wait behind the LOADS of tile t+1: 41 % of its time, ncu round 2)
 //   warps 0-3   softmax + epilogue of even tiles (TMEM set 0)
 //   warps 4-7   softmax + epilogue of odd tiles  (TMEM set 1)
 //   warp 10     TMA store: O tiles leave through the stage's dead Q buffer, one 3-D box per panel
@@ -34,12 +36,16 @@ namespace {
 constexpr int kD = 128;
 constexpr int kSinkKeys = 16;
 constexpr int kMaxWin = 112;
-constexpr int kThreads3 = 352;
+constexpr int kThreads3 = 384;
 constexpr int kQBytes = 2 * 128 * 128;           // [128 packed rows][128 d] bf16, two 64-d panels
 constexpr int kSinkBytes = kSinkKeys * 256;      // K or V sink tile, two panels
 constexpr int kStagesMax = 3;
 constexpr int kSmemBudget = 225 * 1024;
 constexpr uint32_t kColSink = 0, kColWin = 16, kColOut = 128, kColsPerSet = 256;
+// bf16 P: its own columns [80, 120) while the scores fit below them (nW <= 64), so that the next
+// scores of a set may be issued as soon as the softmax has READ the old ones; wider windows overlay
+// P on the score columns and the next scores wait for PV.
+constexpr uint32_t kColPSep = 80;
 
 // barriers: full[3] empty[3] staged[3] sfull[2] pready[2] ofull[2]
 constexpr int bFull = 0, bEmpty = 3, bStaged = 6, bSFull = 9, bPReady = 11, bOFull = 13, kNumBars3 = 15;
@@ -57,6 +63,17 @@ struct Tile {
   int seq_start, r0, n, stream_end, kvh;
   bool valid;
 };
+
+// Developer build: clock64 timeline of the first tiles of a few CTAs (tools/stream_trace.py).
+#ifdef TMX_DEV
+#define TMX_TRACE(ev, t)                                                                              \
+  do {                                                                                                \
+    if (p.trace != nullptr && blockIdx.x < 4 && (t) < 96)                                             \
+      p.trace[((long long)blockIdx.x * 96 + (t)) * 12 + (ev)] = clock64();                            \
+  } while (0)
+#else
+#define TMX_TRACE(ev, t) do { } while (0)
+#endif
 
 // Work item L (KV head fastest) -> tile; identical in every role.
 __device__ __forceinline__ Tile tile_at(const AttnParams& p, unsigned L, int TT) {
@@ -80,6 +97,8 @@ attn_stream3_kernel(const AttnParams p, const __grid_constant__ Stream3Maps maps
   constexpr int winBytes = nW * 256;                          // K or V window tile (two panels)
   constexpr int winPanel = nW * 128;
   constexpr uint32_t stageBytes = (uint32_t)(kQBytes + 2 * winBytes + 2 * kSinkBytes);
+  constexpr bool kSepP = NWC <= 4;
+  constexpr uint32_t kColP = kSepP ? kColPSep : 0u;
   extern __shared__ uint8_t smem_raw[];
   const uint32_t smem_base = (ptx::smem_u32(smem_raw) + 1023u) & ~1023u;
   const uint32_t sBar = smem_base + (uint32_t)n_stages * stageBytes;
@@ -117,6 +136,7 @@ attn_stream3_kernel(const AttnParams p, const __grid_constant__ Stream3Maps maps
         if (!tl.valid) continue;
         const int st = t % n_stages;
         if (t >= n_stages) ptx::mbar_wait(bar(bEmpty + st), ((t / n_stages) - 1) & 1);
+        TMX_TRACE(0, t);
         const uint32_t sQ = stage_base(st), sKw = sQ + kQBytes, sVw = sKw + winBytes;
         const uint32_t sKs = sVw + winBytes, sVs = sKs + kSinkBytes;
         const uint32_t full = bar(bFull + st);
@@ -133,55 +153,62 @@ attn_stream3_kernel(const AttnParams p, const __grid_constant__ Stream3Maps maps
       }
     }
     __syncwarp();
-  } else if (warp == 9) {
-    // =========================== MMA issuer ===========================
+  } else if (warp == 9 || warp == 11) {
+    // =========================== MMA issuers ===========================
     const uint32_t tb = __shfl_sync(0xffffffffu, tmem_base, 0);
     constexpr uint32_t idS16 = ptx::instr_desc_bf16(128, kSinkKeys, false);
     constexpr uint32_t idSW = ptx::instr_desc_bf16(128, nW, false);
     constexpr uint32_t idO = ptx::instr_desc_bf16(128, 128, true);
-    // Scores of local tile t into TMEM set t & 1.  No "set free" wait: S(t) is issued after PV(t-2)
-    // by this same thread (tcgen05 ops execute in issue order), and PV(t-2) itself waited for P(t-2).
-    auto issue_s = [&](int t) {
-      const int st = t % n_stages, set = t & 1;
-      ptx::mbar_wait(bar(bFull + st), (t / n_stages) & 1);
-      ptx::tc_fence_after();
-      if (ptx::elect_one()) {
-        const uint32_t sQ = stage_base(st), sKw = sQ + kQBytes, sKs = sKw + 2 * winBytes;
-        const uint64_t dQ = ptx::smem_desc(sQ, 16, 1024);
-        const uint64_t dKs = ptx::smem_desc(sKs, 16, 1024), dKw = ptx::smem_desc(sKw, 16, 1024);
-        const uint32_t tc = tb + (uint32_t)set * kColsPerSet;
-#pragma unroll
-        for (int ks = 0; ks < 8; ++ks) {
-          const uint32_t qo = ((ks >> 2) * (128 * 128) + (ks & 3) * 32) >> 4;
-          ptx::mma_ss(tc + kColSink, dQ + qo, dKs + (((ks >> 2) * (kSinkKeys * 128) + (ks & 3) * 32) >> 4), idS16, ks > 0);
-          ptx::mma_ss(tc + kColWin, dQ + qo, dKw + (((ks >> 2) * winPanel + (ks & 3) * 32) >> 4), idSW, ks > 0);
-        }
-        ptx::mma_commit(bar(bSFull + set));
-      }
-      __syncwarp();
-    };
     // how many valid tiles does this CTA own?  (same walk as the producer)
     int ntiles = 0;
     for (unsigned L = blockIdx.x; L < n_items; L += gridDim.x) ntiles += tile_at(p, L, TT).valid ? 1 : 0;
     ntiles = __shfl_sync(0xffffffffu, ntiles, 0);
-    if (ntiles > 0) issue_s(0);
-    for (int t = 0; t < ntiles; ++t) {
-      if (t + 1 < ntiles) issue_s(t + 1);
-      const int st = t % n_stages, set = t & 1;
-      // P(t) stored => this group finished reading O(t-2) (its epilogue precedes its next softmax)
-      ptx::mbar_wait(bar(bPReady + set), (t >> 1) & 1);
-      ptx::tc_fence_after();
-      if (ptx::elect_one()) {
-        const uint32_t sVw = stage_base(st) + kQBytes + winBytes, sVs = sVw + winBytes + kSinkBytes;
-        const uint64_t dVs = ptx::smem_desc(sVs, kSinkKeys * 128, 1024), dVw = ptx::smem_desc(sVw, winPanel, 1024);
-        const uint32_t tc = tb + (uint32_t)set * kColsPerSet;
-        ptx::mma_ts(tc + kColOut, tc, dVs, idO, 0);          // sink keys: P columns [0,8)
+    if (warp == 9) {
+      // Scores of local tile t into TMEM set t & 1, as soon as (a) the tile has landed and (b) the set's
+      // score columns are free: the softmax has read S(t-2) (kSepP: "P(t-2) stored" says so), or, when P
+      // overlays the scores, PV(t-2) has consumed it.
+      for (int t = 0; t < ntiles; ++t) {
+        const int st = t % n_stages, set = t & 1;
+        ptx::mbar_wait(bar(bFull + st), (t / n_stages) & 1);
+        TMX_TRACE(1, t);
+        if (t >= 2) ptx::mbar_wait(bar((kSepP ? bPReady : bOFull) + set), ((t >> 1) - 1) & 1);
+        ptx::tc_fence_after();
+        if (ptx::elect_one()) {
+          const uint32_t sQ = stage_base(st), sKw = sQ + kQBytes, sKs = sKw + 2 * winBytes;
+          const uint64_t dQ = ptx::smem_desc(sQ, 16, 1024);
+          const uint64_t dKs = ptx::smem_desc(sKs, 16, 1024), dKw = ptx::smem_desc(sKw, 16, 1024);
+          const uint32_t tc = tb + (uint32_t)set * kColsPerSet;
 #pragma unroll
-        for (int ks = 0; ks < NWC; ++ks)
-          ptx::mma_ts(tc + kColOut, tc + 8 + (uint32_t)(ks * 8), dVw + (uint64_t)((ks * 2048) >> 4), idO, 1);
-        ptx::mma_commit(bar(bOFull + set));
+          for (int ks = 0; ks < 8; ++ks) {
+            const uint32_t qo = ((ks >> 2) * (128 * 128) + (ks & 3) * 32) >> 4;
+            ptx::mma_ss(tc + kColSink, dQ + qo, dKs + (((ks >> 2) * (kSinkKeys * 128) + (ks & 3) * 32) >> 4), idS16, ks > 0);
+            ptx::mma_ss(tc + kColWin, dQ + qo, dKw + (((ks >> 2) * winPanel + (ks & 3) * 32) >> 4), idSW, ks > 0);
+          }
+          ptx::mma_commit(bar(bSFull + set));
+          TMX_TRACE(2, t);
+        }
+        __syncwarp();
       }
-      __syncwarp();
+    } else {
+      for (int t = 0; t < ntiles; ++t) {
+        const int st = t % n_stages, set = t & 1;
+        // P(t) stored => S(t) was issued (V has landed with it) and this group finished reading O(t-2)
+        // (its epilogue precedes its next softmax)
+        ptx::mbar_wait(bar(bPReady + set), (t >> 1) & 1);
+        ptx::tc_fence_after();
+        if (ptx::elect_one()) {
+          const uint32_t sVw = stage_base(st) + kQBytes + winBytes, sVs = sVw + winBytes + kSinkBytes;
+          const uint64_t dVs = ptx::smem_desc(sVs, kSinkKeys * 128, 1024), dVw = ptx::smem_desc(sVw, winPanel, 1024);
+          const uint32_t tc = tb + (uint32_t)set * kColsPerSet;
+          ptx::mma_ts(tc + kColOut, tc + kColP, dVs, idO, 0);          // sink keys: P columns [0,8)
+#pragma unroll
+          for (int ks = 0; ks < NWC; ++ks)
+            ptx::mma_ts(tc + kColOut, tc + kColP + 8 + (uint32_t)(ks * 8), dVw + (uint64_t)((ks * 2048) >> 4), idO, 1);
+          ptx::mma_commit(bar(bOFull + set));
+          TMX_TRACE(5, t);
+        }
+        __syncwarp();
+      }
     }
   } else if (warp == 10) {
     // =========================== TMA store ===========================
@@ -194,6 +221,7 @@ attn_stream3_kernel(const AttnParams p, const __grid_constant__ Stream3Maps maps
         if (!tl.valid) continue;
         const int st = t % n_stages;
         ptx::mbar_wait(bar(bStaged + st), (t / n_stages) & 1);
+        TMX_TRACE(8, t);
         if (tl.r0 + TT <= tl.stream_end) {
           const uint32_t sO = stage_base(st);
           ptx::tma_store_3d(&maps.o, sO, 0, tl.kvh * G, tl.seq_start + tl.r0);
@@ -202,6 +230,7 @@ attn_stream3_kernel(const AttnParams p, const __grid_constant__ Stream3Maps maps
           ptx::bulk_wait_read0();
         }
         ptx::mbar_arrive(bar(bEmpty + st));
+        TMX_TRACE(9, t);
         ++t;
       }
       ptx::bulk_wait_all0();       // global writes complete before the CTA exits
@@ -230,6 +259,7 @@ attn_stream3_kernel(const AttnParams p, const __grid_constant__ Stream3Maps maps
 
       ptx::mbar_wait(bar(bSFull + grp), use & 1);
       ptx::tc_fence_after();
+      if (m == 0) TMX_TRACE(3, t);
       // the whole row at once: 16 sink scores + nW window scores, ONE wait
       uint32_t xs[16];
       uint32_t xw[NWC][16];
@@ -237,54 +267,60 @@ attn_stream3_kernel(const AttnParams p, const __grid_constant__ Stream3Maps maps
 #pragma unroll
       for (int c = 0; c < NWC; ++c) ptx::tmem_ld16(tl + kColWin + (uint32_t)(c * 16), xw[c]);
       ptx::tc_wait_ld();
-      float mx0 = -INFINITY, mx1 = -INFINITY;
+      // mask in place (independent selects), then the row max over 8 independent chains
+      float mxa[8];
 #pragma unroll
-      for (int e = 0; e < 16; e += 2) {
-        mx0 = ((sink_bits >> e) & 1u) ? fmaxf(mx0, __uint_as_float(xs[e])) : mx0;
-        mx1 = ((sink_bits >> (e + 1)) & 1u) ? fmaxf(mx1, __uint_as_float(xs[e + 1])) : mx1;
+      for (int e = 0; e < 8; ++e) mxa[e] = -INFINITY;
+#pragma unroll
+      for (int e = 0; e < 16; ++e) {
+        const float x = ((sink_bits >> e) & 1u) ? __uint_as_float(xs[e]) : -INFINITY;
+        xs[e] = __float_as_uint(x);
+        mxa[e & 7] = fmaxf(mxa[e & 7], x);
       }
 #pragma unroll
       for (int c = 0; c < NWC; ++c) {
         const uint32_t bits = bit_span32(clo - c * 16, chi - c * 16);
 #pragma unroll
-        for (int e = 0; e < 16; e += 2) {
-          mx0 = ((bits >> e) & 1u) ? fmaxf(mx0, __uint_as_float(xw[c][e])) : mx0;
-          mx1 = ((bits >> (e + 1)) & 1u) ? fmaxf(mx1, __uint_as_float(xw[c][e + 1])) : mx1;
+        for (int e = 0; e < 16; ++e) {
+          const float x = ((bits >> e) & 1u) ? __uint_as_float(xw[c][e]) : -INFINITY;
+          xw[c][e] = __float_as_uint(x);
+          mxa[e & 7] = fmaxf(mxa[e & 7], x);
         }
       }
-      const float mx = fmaxf(mx0, mx1);
-      const float msc = (mx == -INFINITY) ? 0.f : mx * sc;
-      float l0 = 0.f, l1 = 0.f;
+      const float mx = fmaxf(fmaxf(fmaxf(mxa[0], mxa[1]), fmaxf(mxa[2], mxa[3])),
+                             fmaxf(fmaxf(mxa[4], mxa[5]), fmaxf(mxa[6], mxa[7])));
+      const float msc = (mx == -INFINITY) ? 0.f : mx * sc;     // (the diagonal is always attended)
+      float la[4] = {0.f, 0.f, 0.f, 0.f};
       {
         uint32_t pk[8];
 #pragma unroll
         for (int e = 0; e < 16; e += 2) {
-          const float a = ((sink_bits >> e) & 1u) ? fast_exp2(fmaf(__uint_as_float(xs[e]), sc, -msc)) : 0.f;
-          const float b = ((sink_bits >> (e + 1)) & 1u) ? fast_exp2(fmaf(__uint_as_float(xs[e + 1]), sc, -msc)) : 0.f;
-          l0 += a; l1 += b;
+          const float a = fast_exp2(fmaf(__uint_as_float(xs[e]), sc, -msc));        // exp2(-inf) = 0
+          const float b = fast_exp2(fmaf(__uint_as_float(xs[e + 1]), sc, -msc));
+          la[(e >> 1) & 3] += a + b;
           pk[e / 2] = pack2s(a, b);
         }
-        ptx::tmem_st8(tl, pk);                     // every score is in registers: P may overwrite S
+        ptx::tmem_st8(tl + kColP, pk);               // every score is in registers: P may overwrite S
       }
 #pragma unroll
       for (int c = 0; c < NWC; ++c) {
-        const uint32_t bits = bit_span32(clo - c * 16, chi - c * 16);
         uint32_t pk[8];
 #pragma unroll
         for (int e = 0; e < 16; e += 2) {
-          const float a = ((bits >> e) & 1u) ? fast_exp2(fmaf(__uint_as_float(xw[c][e]), sc, -msc)) : 0.f;
-          const float b = ((bits >> (e + 1)) & 1u) ? fast_exp2(fmaf(__uint_as_float(xw[c][e + 1]), sc, -msc)) : 0.f;
-          l0 += a; l1 += b;
+          const float a = fast_exp2(fmaf(__uint_as_float(xw[c][e]), sc, -msc));
+          const float b = fast_exp2(fmaf(__uint_as_float(xw[c][e + 1]), sc, -msc));
+          la[(e >> 1) & 3] += a + b;
           pk[e / 2] = pack2s(a, b);
         }
-        ptx::tmem_st8(tl + 8u + (uint32_t)(c * 8), pk);
+        ptx::tmem_st8(tl + kColP + 8u + (uint32_t)(c * 8), pk);
       }
       ptx::tc_wait_st();
       ptx::tc_fence_before();
       __syncwarp();
       if (lane == 0) ptx::mbar_arrive(bar(bPReady + grp));
+      if (m == 0) TMX_TRACE(4, t);
 
-      const float l = l0 + l1;
+      const float l = (la[0] + la[1]) + (la[2] + la[3]);
       const float inv = l > 0.f ? fast_rcp(l) : 0.f;
       // whole tile inside the streamed rows -> TMA store through the stage's (dead) Q buffer
       const bool tma_out = tile.r0 + TT <= tile.stream_end;
@@ -294,6 +330,7 @@ attn_stream3_kernel(const AttnParams p, const __grid_constant__ Stream3Maps maps
         p.lse[(long long)head * p.total_T + tile.seq_start + i] = msc * 0.6931471805599453f + logf(l);
       ptx::mbar_wait(bar(bOFull + grp), use & 1);
       ptx::tc_fence_after();
+      if (m == 0) TMX_TRACE(6, t);
       auto emit = [&](int c, const uint32_t (&r)[32]) {
 #pragma unroll
         for (int v4 = 0; v4 < 4; ++v4) {
@@ -333,6 +370,7 @@ attn_stream3_kernel(const AttnParams p, const __grid_constant__ Stream3Maps maps
       if (tma_out) ptx::fence_proxy_async_smem();           // st.shared -> visible to the TMA store
       __syncwarp();
       if (lane == 0) ptx::mbar_arrive(bar(bStaged + st));    // 4 warps: tile staged (or stored row by row)
+      if (m == 0) TMX_TRACE(7, t);
       ++t;
     }
   }
