@@ -38,7 +38,6 @@ constexpr int kSinkKeys = 16;
 constexpr int kMaxWin = 112;
 constexpr int kThreads3 = 384;
 constexpr int kQBytes = 2 * 128 * 128;           // [128 packed rows][128 d] bf16, two 64-d panels
-constexpr int kSinkBytes = kSinkKeys * 256;      // K or V sink tile, two panels
 constexpr int kStagesMax = 3;
 constexpr int kSmemBudget = 225 * 1024;
 constexpr uint32_t kColSink = 0, kColWin = 16, kColOut = 128, kColsPerSet = 256;
@@ -89,14 +88,19 @@ __device__ __forceinline__ Tile tile_at(const AttnParams& p, unsigned L, int TT)
   return t;
 }
 
-template <int NWC>
+// kDirect: the epilogue writes O straight from registers to global memory (32-byte stores) and the
+// stage returns to the producer when PV completes (tcgen05.commit); otherwise O is staged in the stage's
+// dead Q buffer and leaves by TMA store, and the stage is held until the store has read it.
+template <int NWC, bool kDirect>
 __global__ void __launch_bounds__(kThreads3, 1)
 attn_stream3_kernel(const AttnParams p, const __grid_constant__ Stream3Maps maps, const int G,
                     const int n_stages, const unsigned n_items) {
   constexpr int nW = NWC * 16;
-  constexpr int winBytes = nW * 256;                          // K or V window tile (two panels)
-  constexpr int winPanel = nW * 128;
-  constexpr uint32_t stageBytes = (uint32_t)(kQBytes + 2 * winBytes + 2 * kSinkBytes);
+  // K (and V) of a tile: two 64-d panels of [16 sink keys | nW window keys] rows of 128 bytes, so that the
+  // scores of sink + window are ONE N = 16 + nW MMA per k-step and PV walks 1 + NWC uniform 16-key steps
+  constexpr int kvPanel = (kSinkKeys + nW) * 128;
+  constexpr int kvBytes = 2 * kvPanel;                         // K or V of one tile
+  constexpr uint32_t stageBytes = (uint32_t)(kQBytes + 2 * kvBytes);
   constexpr bool kSepP = NWC <= 4;
   constexpr uint32_t kColP = kSepP ? kColPSep : 0u;
   extern __shared__ uint8_t smem_raw[];
@@ -137,17 +141,16 @@ attn_stream3_kernel(const AttnParams p, const __grid_constant__ Stream3Maps maps
         const int st = t % n_stages;
         if (t >= n_stages) ptx::mbar_wait(bar(bEmpty + st), ((t / n_stages) - 1) & 1);
         TMX_TRACE(0, t);
-        const uint32_t sQ = stage_base(st), sKw = sQ + kQBytes, sVw = sKw + winBytes;
-        const uint32_t sKs = sVw + winBytes, sVs = sKs + kSinkBytes;
+        const uint32_t sQ = stage_base(st), sK = sQ + kQBytes, sV = sK + kvBytes;
         const uint32_t full = bar(bFull + st);
         const int w0 = tl.r0 - p.sl, tok = tl.seq_start + tl.r0;
         ptx::mbar_expect_tx(full, stageBytes);
         for (int pnl = 0; pnl < 2; ++pnl) {
           ptx::tma_load_3d(sQ + pnl * (128 * 128), &maps.q, full, pnl * 64, tl.kvh * G, tok);
-          ptx::tma_load_2d(sKs + pnl * (kSinkKeys * 128), &maps.ks, full, tl.kvh * kD + pnl * 64, tl.seq_start);
-          ptx::tma_load_2d(sKw + pnl * winPanel, &maps.kw, full, tl.kvh * kD + pnl * 64, tl.seq_start + w0);
-          ptx::tma_load_2d(sVs + pnl * (kSinkKeys * 128), &maps.vs, full, tl.kvh * kD + pnl * 64, tl.seq_start);
-          ptx::tma_load_2d(sVw + pnl * winPanel, &maps.vw, full, tl.kvh * kD + pnl * 64, tl.seq_start + w0);
+          ptx::tma_load_2d(sK + pnl * kvPanel, &maps.ks, full, tl.kvh * kD + pnl * 64, tl.seq_start);
+          ptx::tma_load_2d(sK + pnl * kvPanel + kSinkKeys * 128, &maps.kw, full, tl.kvh * kD + pnl * 64, tl.seq_start + w0);
+          ptx::tma_load_2d(sV + pnl * kvPanel, &maps.vs, full, tl.kvh * kD + pnl * 64, tl.seq_start);
+          ptx::tma_load_2d(sV + pnl * kvPanel + kSinkKeys * 128, &maps.vw, full, tl.kvh * kD + pnl * 64, tl.seq_start + w0);
         }
         ++t;
       }
@@ -156,8 +159,7 @@ attn_stream3_kernel(const AttnParams p, const __grid_constant__ Stream3Maps maps
   } else if (warp == 9 || warp == 11) {
     // =========================== MMA issuers ===========================
     const uint32_t tb = __shfl_sync(0xffffffffu, tmem_base, 0);
-    constexpr uint32_t idS16 = ptx::instr_desc_bf16(128, kSinkKeys, false);
-    constexpr uint32_t idSW = ptx::instr_desc_bf16(128, nW, false);
+    constexpr uint32_t idS = ptx::instr_desc_bf16(128, kSinkKeys + nW, false);
     constexpr uint32_t idO = ptx::instr_desc_bf16(128, 128, true);
     // how many valid tiles does this CTA own?  (same walk as the producer)
     int ntiles = 0;
@@ -174,16 +176,13 @@ attn_stream3_kernel(const AttnParams p, const __grid_constant__ Stream3Maps maps
         if (t >= 2) ptx::mbar_wait(bar((kSepP ? bPReady : bOFull) + set), ((t >> 1) - 1) & 1);
         ptx::tc_fence_after();
         if (ptx::elect_one()) {
-          const uint32_t sQ = stage_base(st), sKw = sQ + kQBytes, sKs = sKw + 2 * winBytes;
-          const uint64_t dQ = ptx::smem_desc(sQ, 16, 1024);
-          const uint64_t dKs = ptx::smem_desc(sKs, 16, 1024), dKw = ptx::smem_desc(sKw, 16, 1024);
+          const uint32_t sQ = stage_base(st), sK = sQ + kQBytes;
+          const uint64_t dQ = ptx::smem_desc(sQ, 16, 1024), dK = ptx::smem_desc(sK, 16, 1024);
           const uint32_t tc = tb + (uint32_t)set * kColsPerSet;
 #pragma unroll
-          for (int ks = 0; ks < 8; ++ks) {
-            const uint32_t qo = ((ks >> 2) * (128 * 128) + (ks & 3) * 32) >> 4;
-            ptx::mma_ss(tc + kColSink, dQ + qo, dKs + (((ks >> 2) * (kSinkKeys * 128) + (ks & 3) * 32) >> 4), idS16, ks > 0);
-            ptx::mma_ss(tc + kColWin, dQ + qo, dKw + (((ks >> 2) * winPanel + (ks & 3) * 32) >> 4), idSW, ks > 0);
-          }
+          for (int ks = 0; ks < 8; ++ks)
+            ptx::mma_ss(tc + kColSink, dQ + (((ks >> 2) * (128 * 128) + (ks & 3) * 32) >> 4),
+                        dK + (((ks >> 2) * kvPanel + (ks & 3) * 32) >> 4), idS, ks > 0);
           ptx::mma_commit(bar(bSFull + set));
           TMX_TRACE(2, t);
         }
@@ -197,14 +196,13 @@ attn_stream3_kernel(const AttnParams p, const __grid_constant__ Stream3Maps maps
         ptx::mbar_wait(bar(bPReady + set), (t >> 1) & 1);
         ptx::tc_fence_after();
         if (ptx::elect_one()) {
-          const uint32_t sVw = stage_base(st) + kQBytes + winBytes, sVs = sVw + winBytes + kSinkBytes;
-          const uint64_t dVs = ptx::smem_desc(sVs, kSinkKeys * 128, 1024), dVw = ptx::smem_desc(sVw, winPanel, 1024);
+          const uint64_t dV = ptx::smem_desc(stage_base(st) + kQBytes + kvBytes, kvPanel, 1024);
           const uint32_t tc = tb + (uint32_t)set * kColsPerSet;
-          ptx::mma_ts(tc + kColOut, tc + kColP, dVs, idO, 0);          // sink keys: P columns [0,8)
 #pragma unroll
-          for (int ks = 0; ks < NWC; ++ks)
-            ptx::mma_ts(tc + kColOut, tc + kColP + 8 + (uint32_t)(ks * 8), dVw + (uint64_t)((ks * 2048) >> 4), idO, 1);
+          for (int ks = 0; ks <= NWC; ++ks)          // 16 sink keys, then the window in 16-key steps
+            ptx::mma_ts(tc + kColOut, tc + kColP + (uint32_t)(ks * 8), dV + (uint64_t)((ks * 2048) >> 4), idO, ks > 0);
           ptx::mma_commit(bar(bOFull + set));
+          if constexpr (kDirect) ptx::mma_commit(bar(bEmpty + st));   // Q, K, V of the stage are dead
           TMX_TRACE(5, t);
         }
         __syncwarp();
@@ -214,7 +212,7 @@ attn_stream3_kernel(const AttnParams p, const __grid_constant__ Stream3Maps maps
     // =========================== TMA store ===========================
     // Tiles leave in order; a stage returns to the producer once its O tile has been READ out of
     // shared memory (or at once, for the edge tiles the softmax warps stored row by row).
-    if (ptx::elect_one()) {
+    if (!kDirect && ptx::elect_one()) {
       int t = 0;
       for (unsigned L = blockIdx.x; L < n_items; L += gridDim.x) {
         const Tile tl = tile_at(p, L, TT);
@@ -332,6 +330,21 @@ attn_stream3_kernel(const AttnParams p, const __grid_constant__ Stream3Maps maps
       ptx::tc_fence_after();
       if (m == 0) TMX_TRACE(6, t);
       auto emit = [&](int c, const uint32_t (&r)[32]) {
+        if constexpr (kDirect) {
+          // 32 fp32 columns -> 64 bytes of the row: two 32-byte stores (whole sectors)
+          if (i < tile.stream_end) {
+#pragma unroll
+            for (int v8 = 0; v8 < 2; ++v8) {
+              uint32_t w[8];
+#pragma unroll
+              for (int e = 0; e < 8; ++e)
+                w[e] = pack2s(__uint_as_float(r[v8 * 16 + 2 * e]) * inv, __uint_as_float(r[v8 * 16 + 2 * e + 1]) * inv);
+              asm volatile("st.global.v8.b32 [%0], {%1,%2,%3,%4,%5,%6,%7,%8};" ::"l"(orow + c * 32 + v8 * 16),
+                           "r"(w[0]), "r"(w[1]), "r"(w[2]), "r"(w[3]), "r"(w[4]), "r"(w[5]), "r"(w[6]), "r"(w[7]) : "memory");
+            }
+          }
+          return;
+        }
 #pragma unroll
         for (int v4 = 0; v4 < 4; ++v4) {
           uint4 o;
@@ -339,7 +352,9 @@ attn_stream3_kernel(const AttnParams p, const __grid_constant__ Stream3Maps maps
           o.y = pack2s(__uint_as_float(r[v4 * 8 + 2]) * inv, __uint_as_float(r[v4 * 8 + 3]) * inv);
           o.z = pack2s(__uint_as_float(r[v4 * 8 + 4]) * inv, __uint_as_float(r[v4 * 8 + 5]) * inv);
           o.w = pack2s(__uint_as_float(r[v4 * 8 + 6]) * inv, __uint_as_float(r[v4 * 8 + 7]) * inv);
-          if (tma_out) {
+          if constexpr (kDirect) {
+            (void)o;
+          } else if (tma_out) {
             // 128-byte-swizzled K-major panel layout (what the TMA box expects): 16-byte chunk ch of
             // packed row m lives at m * 128 + ((ch ^ (m & 7)) << 4) inside its 64-d panel
             const int d16 = c * 4 + v4;                     // 16-byte chunk of the 256-byte row
@@ -367,9 +382,11 @@ attn_stream3_kernel(const AttnParams p, const __grid_constant__ Stream3Maps maps
         emit(3, rb);
       }
       ptx::tc_fence_before();
-      if (tma_out) ptx::fence_proxy_async_smem();           // st.shared -> visible to the TMA store
-      __syncwarp();
-      if (lane == 0) ptx::mbar_arrive(bar(bStaged + st));    // 4 warps: tile staged (or stored row by row)
+      if constexpr (!kDirect) {
+        if (tma_out) ptx::fence_proxy_async_smem();           // st.shared -> visible to the TMA store
+        __syncwarp();
+        if (lane == 0) ptx::mbar_arrive(bar(bStaged + st));    // 4 warps: tile staged (or stored row by row)
+      }
       if (m == 0) TMX_TRACE(7, t);
       ++t;
     }
@@ -399,12 +416,20 @@ template <int NWC>
 static int launch_stream3_t(const AttnParams& p, cudaStream_t s) {
   const int G = p.Hq / p.Hkv, TT = 128 / G;
   constexpr int nW = NWC * 16;
-  constexpr int stageBytes = kQBytes + 2 * nW * 256 + 2 * kSinkBytes;
+  constexpr int stageBytes = kQBytes + 4 * (kSinkKeys + nW) * 128;
   int n_stages = (kSmemBudget - 2048) / stageBytes;
   n_stages = n_stages > kStagesMax ? kStagesMax : n_stages;
   if (n_stages < 2) return TMX_ERR_UNSUPPORTED;
   const int smem = n_stages * stageBytes + kNumBars3 * 8 + 16 + 1024;
-  TMX_SET_SMEM_ATTR(attn_stream3_kernel<NWC>, kAttrStream3 + NWC, smem);
+  // O leaves by 32-byte register stores (kDirect).  The TMA-store variant is kept for A/B timing in the
+  // developer build (TMX_SM100_VARIANT bit 0).
+  auto kern = attn_stream3_kernel<NWC, true>;
+  int slot = kAttrStream3 + NWC;
+#ifdef TMX_DEV
+  if (sm100_variant() & 1) { kern = attn_stream3_kernel<NWC, false>; slot = -1; }
+#endif
+  if (slot < 0) TMX_CUDA_TRY(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
+  else TMX_SET_SMEM_ATTR(kern, slot, smem);
   Stream3Maps maps;
   int st = tma_map_q3d(&maps.q, p.q, p.total_T, p.Hq, p.q_stride, G, TT);
   if (st == TMX_OK) st = tma_map_q3d(&maps.o, p.out, p.total_T, p.Hq, p.o_stride, G, TT);
@@ -416,7 +441,7 @@ static int launch_stream3_t(const AttnParams& p, cudaStream_t s) {
   const unsigned n_items = (unsigned)p.n_slots * (unsigned)p.Hkv;
   const unsigned sms = (unsigned)device_sm_count();
   dim3 grid(n_items < sms ? n_items : sms);
-  attn_stream3_kernel<NWC><<<grid, kThreads3, smem, s>>>(p, maps, G, n_stages, n_items);
+  kern<<<grid, kThreads3, smem, s>>>(p, maps, G, n_stages, n_items);
   count_launch();
   TMX_CUDA_TRY(cudaGetLastError());
   return TMX_OK;
