@@ -421,12 +421,14 @@ static int launch_stream3_t(const AttnParams& p, cudaStream_t s) {
   n_stages = n_stages > kStagesMax ? kStagesMax : n_stages;
   if (n_stages < 2) return TMX_ERR_UNSUPPORTED;
   const int smem = n_stages * stageBytes + kNumBars3 * 8 + 16 + 1024;
-  // O leaves by 32-byte register stores (kDirect).  The TMA-store variant is kept for A/B timing in the
-  // developer build (TMX_SM100_VARIANT bit 0).
-  auto kern = attn_stream3_kernel<NWC, true>;
+  // O leaves by TMA store.  Measured round 2 (profiles/r02_stream3_experiments.md): writing it with 32-byte
+  // register stores instead releases the stage 2500 clk earlier but costs 3000 clk of epilogue per tile (one
+  // L1 wavefront per lane at the 256-byte row pitch): 587 vs 500 us.  Kept in the developer build
+  // (TMX_SM100_VARIANT bit 0) for A/B timing.
+  auto kern = attn_stream3_kernel<NWC, false>;
   int slot = kAttrStream3 + NWC;
 #ifdef TMX_DEV
-  if (sm100_variant() & 1) { kern = attn_stream3_kernel<NWC, false>; slot = -1; }
+  if (sm100_variant() & 1) { kern = attn_stream3_kernel<NWC, true>; slot = -1; }
 #endif
   if (slot < 0) TMX_CUDA_TRY(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
   else TMX_SET_SMEM_ATTR(kern, slot, smem);
