@@ -64,7 +64,9 @@ enum { TMX_F32 = 0, TMX_BF16 = 1, TMX_F16 = 2 };
 /* which attention kernel serves tmx_prefill_attn */
 enum { TMX_KERNEL_AUTO = 0,   /* tcgen05 kernel where it applies, else mma.sync */
        TMX_KERNEL_MMA = 1,    /* warp-level mma.sync kernel (also the on-GPU cross-check) */
-       TMX_KERNEL_TCGEN05 = 2 /* tcgen05/TMEM/TMA kernel */ };
+       TMX_KERNEL_TCGEN05 = 2, /* tcgen05/TMEM/TMA kernel, one CTA per two query heads */
+       TMX_KERNEL_TCGEN05_PAIR = 3 /* tcgen05 on CTA pairs (cta_group::2), four query heads of a KV head
+                                      per cluster; needs Hq/Hkv % 4 == 0, else TMX_ERR_UNSUPPORTED */ };
 
 const char* tmx_strerror(int status);
 const char* tmx_last_cuda_error(void);

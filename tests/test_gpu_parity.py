@@ -19,13 +19,15 @@ GOLDEN = os.path.join(os.path.dirname(__file__), "golden")
 with open(os.path.join(GOLDEN, "masks.json")) as f:
     G = json.load(f)
 ATTN = np.load(os.path.join(GOLDEN, "attn_small.npz"))
-KERNELS = ["mma", "tcgen05", "auto"]
+KERNELS = ["mma", "tcgen05", "pair", "auto"]
 
 
 def _skip_unpaired(kernel, hq, hkv):
     # the tcgen05 kernel pairs two query heads of one KV head per CTA
     if kernel == "tcgen05" and (hq // hkv) % 2:
         pytest.skip("tcgen05 kernel needs an even number of query heads per KV head")
+    if kernel == "pair" and (hq // hkv) % 4:
+        pytest.skip("the CTA-pair kernel takes four query heads of a KV head per cluster")
 
 
 @pytest.fixture(scope="module")
@@ -224,7 +226,7 @@ def test_attention_vs_oracle(ops, n, hq, hkv, si, sl, last, mode, kernel):
 
 @pytest.mark.parametrize("kernel", KERNELS)
 def test_attention_bitmask_source_identical(ops, kernel):
-    n, hq, hkv, si, sl, last = 1500, 4, 2, 4, 32, 64
+    n, hq, hkv, si, sl, last = 1500, 4, (1 if kernel == "pair" else 2), 4, 32, 64
     q, k, v = _rand(n, hq, hkv, seed=3)
     cu = torch.tensor([0, n], dtype=torch.int32, device=DEV)
     for mode, piece in ((ops.TRIANGLE, "triangle"), (ops.DENSE_CAUSAL, "dense")):
@@ -248,6 +250,7 @@ def test_attention_varlen(ops, mode, kernel):
     lens = [700, 1, 64, 4500, 129, 2048]
     t = sum(lens)
     hq, hkv, si, sl, last = 8, 2, 4, 32, 64
+    _skip_unpaired(kernel, hq, hkv)
     q, k, v = _rand(t, hq, hkv, seed=11)
     cu_list = [0]
     for n in lens:
@@ -266,6 +269,7 @@ def test_attention_varlen(ops, mode, kernel):
 @pytest.mark.parametrize("kernel", KERNELS)
 def test_attention_peaky_softmax(ops, kernel):
     n, hq, hkv = 1024, 4, 1
+    _skip_unpaired(kernel, hq, hkv)
     q, k, v = _rand(n, hq, hkv, seed=5, qscale=4.0)
     cu = torch.tensor([0, n], dtype=torch.int32, device=DEV)
     for mode in (0, 1):
@@ -295,6 +299,8 @@ def _fuzz_case(seed):
     last = r.choice([0, 1, 2, 64, 64, 64, 65, 129, 300, 513, nmax + 3])
     mode = r.choice([0, 1, 1])
     kernel = r.choice(["auto", "auto", "mma"])
+    if (hq // hkv) % 4 == 0 and r.random() < 0.5:
+        kernel = "pair"
     scale = r.choice([128 ** -0.5, 0.05, 0.2])
     return lens, hq, hkv, si, sl, last, mode, kernel, scale
 

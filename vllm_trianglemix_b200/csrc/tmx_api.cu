@@ -98,6 +98,7 @@ struct Plan {
   int stream_bm;   // tokens per streaming CTA
   int tail_tc;     // dense tail rows on the tcgen05 split-KV path
   int tail_bm;     // query-tile size of the tail path
+  int pair;        // block-index pass on CTA pairs (cta_group::2)
   int n_slots, last_tiles, nsplit_max;
   size_t off_slots, off_part_o, off_part_ml, total;
 };
@@ -116,6 +117,9 @@ Plan make_plan(int B, int total_T, int max_seqlen, int Hq, int Hkv, int si, int 
   Plan pl{};
   const bool pairable = Hkv > 0 && Hq % Hkv == 0 && (Hq / Hkv) % 2 == 0;
   pl.kernel = kernel;
+  // explicit request for the CTA-pair kernel (AUTO's choice between the two tcgen05 kernels: see below)
+  pl.pair = kernel == TMX_KERNEL_TCGEN05_PAIR;
+  if (pl.pair) pl.kernel = kernel = TMX_KERNEL_TCGEN05;
   if (kernel == TMX_KERNEL_AUTO) pl.kernel = (pairable && scale_pos) ? TMX_KERNEL_TCGEN05 : TMX_KERNEL_MMA;
   const bool tri = mode == TMX_MODE_TRIANGLE;
   pl.bn = 64;
@@ -178,8 +182,9 @@ int run_plan(const Plan& pl, AttnParams& p, uint8_t* ws, cudaStream_t s) {
   p.tail_clip = pl.tail_tc ? 1 : 0;
   st = build_slots(slots, pl.n_slots, p, pl.bm, pl.bn, s);
   if (st != TMX_OK) return st;
-  st = (pl.kernel == TMX_KERNEL_TCGEN05) ? launch_attn_sm100_v3(p, sm100_variant() & 127, s)
-                                         : launch_attn_mma(p, pl.bm, s);
+  if (pl.kernel == TMX_KERNEL_TCGEN05 && pl.pair) st = launch_attn_sm100_pair(p, s);
+  else if (pl.kernel == TMX_KERNEL_TCGEN05) st = launch_attn_sm100_v3(p, sm100_variant() & 127, s);
+  else st = launch_attn_mma(p, pl.bm, s);
   if (st != TMX_OK || !pl.tail_tc) return st;
   return launch_attn_tail_tc(p, s);
 }
@@ -237,7 +242,7 @@ int check_common(int B, int total_T, int max_seqlen, int Hq, int Hkv, int D, int
                  int64_t kv_stride_t, int64_t o_stride_t, int mode, int kernel) {
   if (B < 0 || total_T < 0 || max_seqlen < 0 || Hq <= 0 || Hkv <= 0) return TMX_ERR_BAD_ARG;
   if (mode < TMX_MODE_DENSE_CAUSAL || mode > TMX_MODE_NONE) return TMX_ERR_BAD_ARG;
-  if (kernel < TMX_KERNEL_AUTO || kernel > TMX_KERNEL_TCGEN05) return TMX_ERR_BAD_ARG;
+  if (kernel < TMX_KERNEL_AUTO || kernel > TMX_KERNEL_TCGEN05_PAIR) return TMX_ERR_BAD_ARG;
   if (D != 128 || Hq % Hkv != 0) return TMX_ERR_BAD_SHAPE;
   if (q_stride_t < (int64_t)Hq * D || kv_stride_t < (int64_t)Hkv * D || o_stride_t < (int64_t)Hq * D)
     return TMX_ERR_BAD_SHAPE;
@@ -269,7 +274,7 @@ extern "C" int tmx_prefill_attn(void* out, const void* q, const void* k, const v
   const float scale_log2 = scale * 1.4426950408889634f;
   const bool scale_pos = scale_log2 > 0.f;
   // an explicit tcgen05 request cannot be served with a non-positive scale; AUTO falls back to mma.sync
-  if (kernel == TMX_KERNEL_TCGEN05 && !scale_pos) return TMX_ERR_UNSUPPORTED;
+  if (kernel >= TMX_KERNEL_TCGEN05 && !scale_pos) return TMX_ERR_UNSUPPORTED;
   Plan pl = make_plan(B, total_T, max_seqlen, Hq, Hkv, si, sl, last, mode, kernel, bitmask != nullptr,
                       scale_pos, false);
   if (!workspace || workspace_bytes < pl.total || misaligned(workspace)) return TMX_ERR_WORKSPACE;
@@ -311,7 +316,7 @@ extern "C" int tmx_chunked_prefill_attn(void* out, const void* q, const int32_t*
   if (st != TMX_OK) return st;
   const float scale_log2 = scale * 1.4426950408889634f;
   const bool scale_pos = scale_log2 > 0.f;
-  if (kernel == TMX_KERNEL_TCGEN05 && !scale_pos) return TMX_ERR_UNSUPPORTED;
+  if (kernel >= TMX_KERNEL_TCGEN05 && !scale_pos) return TMX_ERR_UNSUPPORTED;
   Plan pl = make_plan(B, total_Tq, max_query_len, Hq, Hkv, si, sl, last, mode, kernel, false, scale_pos, true);
   if (!workspace || workspace_bytes < pl.total || misaligned(workspace)) return TMX_ERR_WORKSPACE;
 

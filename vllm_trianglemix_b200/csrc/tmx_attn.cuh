@@ -57,6 +57,9 @@ bool stream_supported(int Hq, int Hkv, int si, int sl);
 int stream_block_m(int Hq, int Hkv);
 int launch_attn_stream3(const AttnParams& p, cudaStream_t s);   // persistent, pipelined
 int launch_attn_sm100_v3(const AttnParams& p, int variant, cudaStream_t s);   // 128-key tiles
+// CTA-pair kernel (cta_group::2): GQA ratios that are multiples of 4 (tmx_attn_sm100_pair.cu)
+bool pair_supported(const AttnParams& p);
+int launch_attn_sm100_pair(const AttnParams& p, cudaStream_t s);
 // dense tail rows of triangle layers on the tensor cores (split-KV + merge, tmx_attn_sm100_v3.cu)
 bool tail_tc_supported(int Hq, int Hkv, float scale_log2);
 int tail_tc_block_m(int Hq, int Hkv);

@@ -1,0 +1,427 @@
+// Masked GQA prefill attention on CTA PAIRS (tcgen05 cta_group::2): the dense-layer kernel of round 2.
+//
+// Round 1's kernel (tmx_attn_sm100_v3.cu) runs one CTA per (128-token query tile, two query heads of a
+// KV head).  ncu showed its shared memory saturated: per tile and CTA the tensor pipe reads 192 KB of
+// operands (Q and K for the scores, V for PV, twice) and TMA writes 64 KB, against 2048 clk of MMA math.
+// Here the two CTAs of a cluster (one TPC) take FOUR query heads of a KV head for the same query tile and
+// issue every MMA as one M = 256 instruction across both SMs (UTCHMMA.2CTA):
+//   S_g = [Q_g(cta0); Q_g(cta1)] K^T   each CTA holds HALF of the K tile (64 keys): B is split along N
+//   O_g += [P_g(cta0); P_g(cta1)] V    each CTA holds HALF of V's columns (one 64-d panel)
+// so a CTA loads 32 KB instead of 64 KB per KV tile and the tensor pipe reads 128 KB instead of 192 KB
+// of shared memory per tile; K/V leave L2 once per FOUR query heads.
+//
+// Roles per CTA (10 warps, as in v3): warps 0-3 / 4-7 softmax group A / B (one thread per query row of
+// head 2*rank / 2*rank+1), warp 8 TMA producer (its halves; byte counts land on the LEADER's barriers),
+// warp 9 MMA issuer (leader CTA only; the peer's warp 9 only takes part in the TMEM allocation).
+// TMEM (512 columns per CTA): S_A | S_B | O_A | O_B; bf16 P overwrites columns [0,64) of its S buffer.
+// Issue order S_A(0) S_B(0) { PV_A(j) S_A(j+1) PV_B(j) S_B(j+1) }_j; MMA completions are multicast to both
+// CTAs' barriers (UTCBAR.2CTA.MULTICAST); "P stored" arrives on the leader's barrier from all 8 warps of a
+// group (4 local, 4 remote).
+//
+// Replaces vllm/attention/ascend_trianglemix.py:86-106 of the reference for dense-causal layers (and any
+// block-index triangle setting) when the GQA ratio is a multiple of 4.
+#include "tmx_attn.cuh"
+#include "tmx_sm100_ptx.cuh"
+#include "tmx_tma.cuh"
+
+namespace tmx {
+namespace {
+
+constexpr int kD = 128;
+constexpr int kBM = 128;
+constexpr int kBN = 128;
+constexpr int kThreads = 320;
+constexpr int kQBytes = 2 * 2 * kBM * 128;        // 2 heads x 2 panels of [128 rows][64 d] = 64 KB per CTA
+constexpr int kKPanel = (kBN / 2) * 128;          // this CTA's 64 keys x 64 d = 8 KB
+constexpr int kItemBytes = 2 * kKPanel;           // K half (64 keys x 128 d) or V half (128 keys x 64 d): 16 KB
+constexpr int kStages = 10;
+constexpr int kOffRing = kQBytes;
+constexpr int kOffBar = kOffRing + kStages * kItemBytes;
+
+constexpr int bQFull = 0;
+constexpr int bFull = 1;                          // [kStages]  (leader's count the bytes of both CTAs)
+constexpr int bEmpty = bFull + kStages;           // [kStages]
+constexpr int bSFull = bEmpty + kStages;          // [2 groups]
+constexpr int bPReady = bSFull + 2;               // [2 groups], leader: 8 arrivals (4 warps x 2 CTAs)
+constexpr int bOFull = bPReady + 2;               // [2 groups]
+constexpr int kNumBars = bOFull + 2;
+constexpr int kSmem = kOffBar + kNumBars * 8 + 16 + 1024;   // + alignment slack
+static_assert(kSmem <= 232448, "exceeds the 227 KB of shared memory a CTA may use");
+
+constexpr uint32_t kColS = 0;      // + g * 128
+constexpr uint32_t kColO = 256;    // + g * 128
+
+struct PairMaps {
+  CUtensorMap q, k, v;             // boxes: 128 rows (q), 64 rows (k half), 128 rows (v half)
+};
+
+__device__ __forceinline__ uint32_t pack2(float lo, float hi) {
+  __nv_bfloat162 v = __floats2bfloat162_rn(lo, hi);
+  return *reinterpret_cast<uint32_t*>(&v);
+}
+// packed fp32 pairs (Blackwell FFMA2 / FADD2)
+__device__ __forceinline__ uint64_t pk_f2(float lo, float hi) {
+  uint64_t r;
+  asm("mov.b64 %0, {%1, %2};" : "=l"(r) : "f"(lo), "f"(hi));
+  return r;
+}
+__device__ __forceinline__ void upk_f2(uint64_t v, float& lo, float& hi) {
+  asm("mov.b64 {%0, %1}, %2;" : "=f"(lo), "=f"(hi) : "l"(v));
+}
+__device__ __forceinline__ uint64_t ffma2(uint64_t a, uint64_t b, uint64_t c) {
+  uint64_t d;
+  asm("fma.rn.f32x2 %0, %1, %2, %3;" : "=l"(d) : "l"(a), "l"(b), "l"(c));
+  return d;
+}
+__device__ __forceinline__ uint64_t fadd2(uint64_t a, uint64_t b) {
+  uint64_t d;
+  asm("add.rn.f32x2 %0, %1, %2;" : "=l"(d) : "l"(a), "l"(b));
+  return d;
+}
+// 2^t on the FMA/ALU pipes for a pair (Cody-Waite split + cubic, max rel. error 7.5e-5)
+__device__ __forceinline__ uint64_t exp2_poly2(uint64_t t2) {
+  float t0, t1;
+  upk_f2(t2, t0, t1);
+  t2 = pk_f2(fmaxf(t0, -126.0f), fmaxf(t1, -126.0f));
+  const uint64_t magic = pk_f2(12582912.0f, 12582912.0f), nmagic = pk_f2(-12582912.0f, -12582912.0f);
+  const uint64_t r2 = fadd2(t2, magic);
+  const uint64_t u2 = fadd2(r2, nmagic);
+  const uint64_t f2 = ffma2(u2, pk_f2(-1.0f, -1.0f), t2);
+  uint64_t pl = ffma2(pk_f2(0.0551716685f, 0.0551716685f), f2, pk_f2(0.2426111251f, 0.2426111251f));
+  pl = ffma2(pl, f2, pk_f2(0.6932609677f, 0.6932609677f));
+  pl = ffma2(pl, f2, pk_f2(0.9999280572f, 0.9999280572f));
+  float p0, p1, r0, r1;
+  upk_f2(pl, p0, p1);
+  upk_f2(r2, r0, r1);
+  p0 = __int_as_float(__float_as_int(p0) + (__float_as_int(r0) << 23));
+  p1 = __int_as_float(__float_as_int(p1) + (__float_as_int(r1) << 23));
+  return pk_f2(p0, p1);
+}
+
+// kEmu: how many of every 16 exponentials run on the FMA pipe (even: 0, 4, 6, 8).
+template <int kEmu>
+__global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kThreads, 1)
+attn_sm100_pair_kernel(const AttnParams p, const __grid_constant__ PairMaps maps) {
+  extern __shared__ uint8_t smem_raw[];
+  const uint32_t smem_base = (ptx::smem_u32(smem_raw) + 1023u) & ~1023u;   // SWIZZLE_128B: 1024-byte atoms
+  const uint32_t sQ = smem_base, sRing = smem_base + kOffRing;
+  const uint32_t sBar = smem_base + kOffBar;
+  const uint32_t sTmemPtr = sBar + kNumBars * 8;
+  auto bar = [&](int i) { return sBar + 8u * (uint32_t)i; };
+
+  const int warp = __shfl_sync(0xffffffffu, (int)(threadIdx.x >> 5), 0);   // provably warp-uniform
+  const int lane = threadIdx.x & 31;
+  const uint32_t rank = ptx::cluster_ctarank();                           // 0 = leader
+  const bool leader = rank == 0;
+
+  // ---- work item: uniform per PAIR (both CTAs read the same slot) ---------------------------
+  // r0 / r1 / i are ABSOLUTE rows of the (context + chunk) sequence (see tmx_attn_sm100_v3.cu).
+  const SlotInfo slot = p.slots[p.n_slots - 1 - (blockIdx.x >> 1)];        // descending: longest first
+  const bool active = slot.seq >= 0;
+  int n = 0, r0 = 0, r1 = -1, lo0 = 0, cnt0 = 0, lo1 = 0, total = 0, seq_start = 0, q_row0 = 0, k_start = 0, lrow = 0;
+  if (active) {
+    const SeqGeom gm = seq_geom(p, slot.seq);
+    n = slot.n; r0 = gm.ctx + slot.q_tile * kBM;
+    r1 = min(n, r0 + kBM) - 1;
+    lrow = first_dense_row(n, p.last);
+    if (p.tail_clip && p.mode == TMX_MODE_TRIANGLE && lrow < n) r1 = min(r1, lrow - 1);
+    lo0 = slot.lo0; cnt0 = slot.hi0 - slot.lo0; lo1 = slot.lo1;
+    total = cnt0 + (slot.hi1 - slot.lo1);
+    seq_start = gm.q_start - gm.ctx;      // query-buffer row of absolute row 0 (may be negative)
+    q_row0 = gm.q_start + slot.q_tile * kBM; k_start = gm.k_start;
+  }
+  if (!active) return;                                 // both CTAs of the pair agree
+  const int h0 = 4 * blockIdx.y + 2 * (int)rank;      // this CTA's two query heads
+  const int kvh = (4 * blockIdx.y) / (p.Hq / p.Hkv);
+  auto tile_of = [&](int it) { return it < cnt0 ? lo0 + it : lo1 + (it - cnt0); };
+
+  // ---- setup -------------------------------------------------------------------
+  if (warp == 8 && lane == 0) {
+    ptx::prefetch_tmap(&maps.q); ptx::prefetch_tmap(&maps.k); ptx::prefetch_tmap(&maps.v);
+    ptx::mbar_init(bar(bQFull), 1);
+    for (int s = 0; s < kStages; ++s) { ptx::mbar_init(bar(bFull + s), 1); ptx::mbar_init(bar(bEmpty + s), 1); }
+    for (int g = 0; g < 2; ++g) {
+      ptx::mbar_init(bar(bSFull + g), 1);
+      ptx::mbar_init(bar(bPReady + g), 8);       // one arrive per softmax warp of the group, both CTAs
+      ptx::mbar_init(bar(bOFull + g), 1);
+    }
+    ptx::fence_barrier_init();
+  }
+  if (warp == 9) ptx::tmem_alloc_pair(sTmemPtr, 512);
+  ptx::tc_fence_before();
+  ptx::cluster_sync();                            // barriers of BOTH CTAs exist before any remote arrive / TMA
+  ptx::tc_fence_after();
+  uint32_t tmem_base;
+  asm volatile("ld.shared.b32 %0, [%1];" : "=r"(tmem_base) : "r"(sTmemPtr));
+
+  if (warp == 8) {
+    // =========================== TMA producer (both CTAs) ===========================
+    // Item t: even = K(t/2), odd = V(t/2).  This CTA's half: keys [64 rank, 64 rank + 64) of the K tile
+    // (both d panels), d panel `rank` of the V tile (all 128 keys).  Bytes are counted on the leader's barrier.
+    if (ptx::elect_one()) {
+      if (leader) ptx::mbar_expect_tx(bar(bQFull), 2 * kQBytes);
+      for (int g = 0; g < 2; ++g)
+        for (int pnl = 0; pnl < 2; ++pnl)
+          ptx::tma_load_2d_pair(sQ + (g * 2 + pnl) * (kBM * 128), &maps.q, bar(bQFull), (h0 + g) * kD + pnl * 64, q_row0);
+      const int items = 2 * total;
+      int st = 0;
+      for (int t = 0; t < items; ++t) {
+        if (t >= kStages) ptx::mbar_wait(bar(bEmpty + st), ((t / kStages) - 1) & 1);
+        if (leader) ptx::mbar_expect_tx(bar(bFull + st), 2 * kItemBytes);
+        const int row = k_start + tile_of(t >> 1) * kBN;
+        const uint32_t dst = sRing + st * kItemBytes;
+        if ((t & 1) == 0) {
+          for (int pnl = 0; pnl < 2; ++pnl)
+            ptx::tma_load_2d_pair(dst + pnl * kKPanel, &maps.k, bar(bFull + st), kvh * kD + pnl * 64, row + 64 * (int)rank);
+        } else {
+          ptx::tma_load_2d_pair(dst, &maps.v, bar(bFull + st), kvh * kD + 64 * (int)rank, row);
+        }
+        if (++st == kStages) st = 0;
+      }
+    }
+    __syncwarp();
+  } else if (warp == 9) {
+    // =========================== MMA issuer (leader CTA only) ===========================
+    if (leader) {
+      const uint32_t tb = __shfl_sync(0xffffffffu, tmem_base, 0);
+      const int ntot = __shfl_sync(0xffffffffu, total, 0);
+      constexpr uint32_t kIdescS = ptx::instr_desc_bf16(256, kBN, false);
+      constexpr uint32_t kIdescO = ptx::instr_desc_bf16(256, 128, true);
+      const uint64_t dQ = ptx::smem_desc(sQ, 16, 1024);
+      const uint64_t dK = ptx::smem_desc(sRing, 16, 1024);             // K half: K-major (d contiguous)
+      const uint64_t dV = ptx::smem_desc(sRing, kItemBytes, 1024);     // V half: MN-major, one 64-d panel
+
+      // S_g = Q_g K^T of the K tile in ring stage `st`: 8 k-steps of 16 over d (two 64-d panels)
+      auto issue_s = [&](int g, int st) {
+        const uint32_t d_tmem = tb + kColS + (uint32_t)(g * 128);
+        const uint64_t qa = dQ + (uint64_t)((g * 2 * (kBM * 128)) >> 4);
+        const uint64_t kb = dK + (uint64_t)((st * kItemBytes) >> 4);
+#pragma unroll
+        for (int ks = 0; ks < 8; ++ks) {
+          const uint32_t qo = ((ks >> 2) * (kBM * 128) + (ks & 3) * 32) >> 4;
+          const uint32_t ko = ((ks >> 2) * kKPanel + (ks & 3) * 32) >> 4;
+          ptx::mma_ss_pair(d_tmem, qa + qo, kb + ko, kIdescS, ks > 0);
+        }
+      };
+      // O_g += P_g V: 8 k-steps of 16 keys; P (bf16) read from columns [0,64) of S_g
+      auto issue_pv = [&](int g, int st, bool acc) {
+        const uint32_t d_tmem = tb + kColO + (uint32_t)(g * 128);
+        const uint32_t a_tmem = tb + kColS + (uint32_t)(g * 128);
+        const uint64_t vb = dV + (uint64_t)((st * kItemBytes) >> 4);
+#pragma unroll
+        for (int ks = 0; ks < kBN / 16; ++ks)
+          ptx::mma_ts_pair(d_tmem, a_tmem + (uint32_t)(ks * 8), vb + (uint64_t)((ks * 2048) >> 4), kIdescO,
+                           acc || ks > 0);
+      };
+
+      int st = 0, ph = 0;                               // ring position of the next item to consume
+      auto advance = [&] { if (++st == kStages) { st = 0; ph ^= 1; } };
+      ptx::mbar_wait_cluster(bar(bQFull), 0);
+      ptx::mbar_wait_cluster(bar(bFull + 0), 0);        // K(0)
+      ptx::tc_fence_after();
+      if (ptx::elect_one()) {
+        issue_s(0, 0); ptx::mma_commit_pair(bar(bSFull + 0));
+        issue_s(1, 0); ptx::mma_commit_pair(bar(bSFull + 1));
+        ptx::mma_commit_pair(bar(bEmpty + 0));
+      }
+      __syncwarp();
+      advance();
+      for (int j = 0; j < ntot; ++j) {
+        const int vst = st, vph = ph;
+        advance();
+        const int kst = st, kph = ph;
+        const bool more = j + 1 < ntot;
+        if (more) advance();
+        ptx::mbar_wait_cluster(bar(bFull + vst), vph);
+#pragma unroll
+        for (int g = 0; g < 2; ++g) {
+          ptx::mbar_wait_cluster(bar(bPReady + g), j & 1);
+          ptx::tc_fence_after();
+          if (ptx::elect_one()) {
+            issue_pv(g, vst, j > 0);
+            if (!more) ptx::mma_commit_pair(bar(bOFull + g));
+            if (g == 1) ptx::mma_commit_pair(bar(bEmpty + vst));
+          }
+          __syncwarp();
+          if (more) {
+            if (g == 0) { ptx::mbar_wait_cluster(bar(bFull + kst), kph); ptx::tc_fence_after(); }
+            if (ptx::elect_one()) {
+              issue_s(g, kst);
+              ptx::mma_commit_pair(bar(bSFull + g));
+              if (g == 1) ptx::mma_commit_pair(bar(bEmpty + kst));
+            }
+            __syncwarp();
+          }
+        }
+      }
+    }
+  } else {
+    // =========================== softmax groups (both CTAs) ===========================
+    const int g = warp >> 2;                       // 0: head h0, 1: head h0 + 1
+    const int row_in_tile = (warp & 3) * 32 + lane;
+    const int i = r0 + row_in_tile;                // query row inside the sequence
+    const int head = h0 + g;
+    const uint32_t lane_base = (uint32_t)((warp & 3) * 32) << 16;
+    const uint32_t tS = tmem_base + lane_base + kColS + (uint32_t)(g * 128);
+    const uint32_t tO = tmem_base + lane_base + kColO + (uint32_t)(g * 128);
+    const float sc = p.scale_log2;                 // > 0 (checked by the launcher)
+    float m_ref = -INFINITY, l_run = 0.f;          // running max (scaled, log2 domain) and row sum
+    const uint32_t* bm_row = p.bitmask ? p.bitmask + (long long)min(i, n - 1) * p.bitmask_stride : nullptr;
+    const uint64_t sc2 = pk_f2(sc, sc);
+
+    for (int j = 0; j < total; ++j) {
+      ptx::mbar_wait(bar(bSFull + g), j & 1);
+      ptx::tc_fence_after();
+      const int c0 = tile_of(j) * kBN;
+      const bool full = bm_row == nullptr &&
+                        tile_is_full(r0, r1, c0, c0 + kBN - 1, n, lrow, p.si, p.sl, p.mode);
+      uint32_t pk[64];             // the row's 128 probabilities as bf16 pairs
+      uint64_t sum2;               // two partial row sums
+      // Optimistic single pass over S: exponentiate against the CURRENT reference max while tracking the
+      // tile's max.  Only if some row's max outgrew the reference by more than 2^8 (always on the first
+      // tile, rarely afterwards) the reference is refreshed, O and l are rescaled and the pass is redone
+      // -- S is still intact in TMEM because P is stored last.
+#pragma unroll 1
+      for (int attempt = 0;; ++attempt) {
+        const float neg_m = (m_ref == -INFINITY) ? 0.f : -m_ref;
+        const uint64_t negm2 = pk_f2(neg_m, neg_m);
+        float mx0 = -INFINITY, mx1 = -INFINITY;
+        sum2 = pk_f2(0.f, 0.f);
+        // 32 scores (columns c0 + 32c ...) -> 16 packed bf16 pairs
+        auto chunk = [&](int c, uint32_t (&xr)[32]) {
+          float x[32];
+#pragma unroll
+          for (int e = 0; e < 32; ++e) x[e] = __uint_as_float(xr[e]);
+          if (!full) {
+            const int cb = c0 + c * 32;
+            const uint32_t bits = bm_row != nullptr ? bm_row[cb >> 5]
+                                                    : mask_word32(i, cb, n, lrow, p.si, p.sl, p.mode);
+#pragma unroll
+            for (int e = 0; e < 32; ++e) x[e] = ((bits >> e) & 1u) ? x[e] : -INFINITY;
+          }
+#pragma unroll
+          for (int e = 0; e < 32; e += 4) {
+            mx0 = fmaxf(mx0, fmaxf(x[e], x[e + 1]));
+            mx1 = fmaxf(mx1, fmaxf(x[e + 2], x[e + 3]));
+          }
+#pragma unroll
+          for (int e = 0; e < 32; e += 2) {
+            uint64_t q2 = ffma2(pk_f2(x[e], x[e + 1]), sc2, negm2);
+            float a, b;
+            if ((e & 15) < kEmu) {
+              q2 = exp2_poly2(q2);
+              upk_f2(q2, a, b);
+            } else {
+              upk_f2(q2, a, b);
+              a = fast_exp2(a);
+              b = fast_exp2(b);
+              q2 = pk_f2(a, b);
+            }
+            sum2 = fadd2(sum2, q2);
+            pk[c * 16 + e / 2] = pack2(a, b);
+          }
+        };
+        uint32_t xa[32], xb[32];
+        ptx::tmem_ld32(tS, xa);
+        ptx::tc_wait_ld();
+        ptx::tmem_ld32(tS + 32, xb);        // in flight while chunk 0 is processed
+        chunk(0, xa);
+        ptx::tc_wait_ld();
+        ptx::tmem_ld32(tS + 64, xa);
+        chunk(1, xb);
+        ptx::tc_wait_ld();
+        ptx::tmem_ld32(tS + 96, xb);
+        chunk(2, xa);
+        ptx::tc_wait_ld();
+        chunk(3, xb);
+        const float m_new = fmaxf(m_ref, fmaxf(mx0, mx1) * sc);
+        const bool grow = (m_new > m_ref + 8.0f) || (m_ref == -INFINITY && m_new > -INFINITY);
+        if (attempt == 1 || !__any_sync(0xffffffffu, grow)) break;
+        if (j > 0) {
+          // S(j) complete => PV(j-1) complete (commit order); PV(j) waits for our arrive below
+          const float alpha = (m_new == -INFINITY) ? 1.0f : fast_exp2(m_ref - m_new);   // m_ref=-inf -> 0
+          l_run *= alpha;
+#pragma unroll
+          for (int c = 0; c < 4; ++c) {
+            uint32_t r[32];
+            ptx::tmem_ld32(tO + c * 32, r);
+            ptx::tc_wait_ld();
+#pragma unroll
+            for (int e = 0; e < 32; ++e) r[e] = __float_as_uint(__uint_as_float(r[e]) * alpha);
+            ptx::tmem_st32(tO + c * 32, r);
+          }
+          ptx::tc_wait_st();
+        }
+        m_ref = m_new;
+      }
+      {
+        float a, b;
+        upk_f2(sum2, a, b);
+        l_run += a + b;
+      }
+      // bf16 P into columns [0,64) of S (every score of the tile has been read by now)
+      ptx::tmem_st32(tS, *reinterpret_cast<uint32_t(*)[32]>(&pk[0]));
+      ptx::tmem_st32(tS + 32, *reinterpret_cast<uint32_t(*)[32]>(&pk[32]));
+      ptx::tc_wait_st();
+      ptx::tc_fence_before();
+      __syncwarp();
+      if (lane == 0) ptx::mbar_arrive_leader(bar(bPReady + g));
+    }
+    // ---- epilogue: O / l -> bf16 -> global ------------------------------------
+    ptx::mbar_wait(bar(bOFull + g), 0);
+    ptx::tc_fence_after();
+    const float inv = l_run > 0.f ? fast_rcp(l_run) : 0.f;
+    __nv_bfloat16* orow = p.out + (long long)(seq_start + i) * p.o_stride + head * kD;   // seq_start + i = query row
+#pragma unroll
+    for (int c = 0; c < 4; ++c) {
+      uint32_t r[32];
+      ptx::tmem_ld32(tO + c * 32, r);
+      ptx::tc_wait_ld();
+      if (i <= r1) {
+#pragma unroll
+        for (int v4 = 0; v4 < 4; ++v4) {
+          uint4 o;
+          o.x = pack2(__uint_as_float(r[v4 * 8 + 0]) * inv, __uint_as_float(r[v4 * 8 + 1]) * inv);
+          o.y = pack2(__uint_as_float(r[v4 * 8 + 2]) * inv, __uint_as_float(r[v4 * 8 + 3]) * inv);
+          o.z = pack2(__uint_as_float(r[v4 * 8 + 4]) * inv, __uint_as_float(r[v4 * 8 + 5]) * inv);
+          o.w = pack2(__uint_as_float(r[v4 * 8 + 6]) * inv, __uint_as_float(r[v4 * 8 + 7]) * inv);
+          *reinterpret_cast<uint4*>(orow + c * 32 + v4 * 8) = o;
+        }
+      }
+    }
+    if (p.lse != nullptr && i <= r1)
+      p.lse[(long long)head * p.total_T + seq_start + i] = m_ref * 0.6931471805599453f + logf(l_run);
+    ptx::tc_fence_before();
+  }
+
+  // ---- teardown: neither CTA may leave (or free TMEM) while its peer still reads its memory ----------
+  ptx::cluster_sync();
+  if (warp == 9) {
+    ptx::tc_fence_after();
+    ptx::tmem_dealloc_pair(tmem_base, 512);
+  }
+}
+
+}  // namespace
+
+bool pair_supported(const AttnParams& p) {
+  return p.Hkv > 0 && p.Hq % p.Hkv == 0 && (p.Hq / p.Hkv) % 4 == 0 && p.scale_log2 > 0.f && p.block_table == nullptr;
+}
+
+int launch_attn_sm100_pair(const AttnParams& p, cudaStream_t s) {
+  if (!pair_supported(p)) return TMX_ERR_UNSUPPORTED;
+  auto kern = attn_sm100_pair_kernel<4>;
+  TMX_SET_SMEM_ATTR(kern, kAttrV3Pair, kSmem);
+  PairMaps maps;
+  int st = tma_map_2d(&maps.q, p.q, p.total_T, (long long)p.Hq * kD, p.q_stride, kBM);
+  if (st == TMX_OK) st = tma_map_2d(&maps.k, p.k, p.total_kv, (long long)p.Hkv * kD, p.kv_stride, kBN / 2);
+  if (st == TMX_OK) st = tma_map_2d(&maps.v, p.v, p.total_kv, (long long)p.Hkv * kD, p.kv_stride, kBN);
+  if (st != TMX_OK) return st;
+  dim3 grid((unsigned)(2 * p.n_slots), (unsigned)(p.Hq / 4));     // clusters of 2 along x
+  kern<<<grid, kThreads, kSmem, s>>>(p, maps);
+  count_launch();
+  TMX_CUDA_TRY(cudaGetLastError());
+  return TMX_OK;
+}
+
+}  // namespace tmx

@@ -14,7 +14,7 @@ from . import _lib
 
 DENSE_CAUSAL, TRIANGLE, NONE = 0, 1, 2
 PIECES = {"streaming": 0, "last": 1, "middle": 2, "triangle": 3, "dense": 4}
-KERNELS = {"auto": 0, "mma": 1, "tcgen05": 2}
+KERNELS = {"auto": 0, "mma": 1, "tcgen05": 2, "pair": 3}
 _DTYPES = {torch.float32: 0, torch.bfloat16: 1, torch.float16: 2}
 
 
