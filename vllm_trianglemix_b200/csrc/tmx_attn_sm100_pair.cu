@@ -44,7 +44,9 @@ constexpr int bEmpty = bFull + kStages;           // [kStages]
 constexpr int bSFull = bEmpty + kStages;          // [2 groups]
 constexpr int bPReady = bSFull + 2;               // [2 groups], leader: 8 arrivals (4 warps x 2 CTAs)
 constexpr int bOFull = bPReady + 2;               // [2 groups]
-constexpr int kNumBars = bOFull + 2;
+constexpr int bH1Read = bOFull + 2;               // [2 groups] kAhead: H1's column block has been read (leader: 8 arrivals)
+constexpr int bH0Full = bH1Read + 2;              // [2 groups] kAhead: first 64 keys of S(j) complete
+constexpr int kNumBars = bH0Full + 2;
 constexpr int kSmem = kOffBar + kNumBars * 8 + 16 + 1024;   // + alignment slack
 static_assert(kSmem <= 232448, "exceeds the 227 KB of shared memory a CTA may use");
 
@@ -99,7 +101,13 @@ __device__ __forceinline__ uint64_t exp2_poly2(uint64_t t2) {
 }
 
 // kEmu: how many of every 16 exponentials run on the FMA pipe (even: 0, 4, 6, 8).
-template <int kEmu>
+// kAhead: the look-ahead schedule of tmx_attn_sm100_v3.cu (kSm == 3) on CTA pairs -- the score MMA of a tile
+// is issued as two 64-key halves H0 | H1 into the two 64-column blocks of the group's S buffer, the blocks
+// swapping roles every tile (P(j) overwrites H0(j)'s block); H0(j+1) is issued as soon as both CTAs' softmax
+// warps have read H1(j) -- before P(j) exists -- and H1(j+1) follows PV(j).  The softmax pass is software-
+// pipelined over its four 32-column chunks.  Each CTA then holds keys {32 rank .. +31} of BOTH halves of the
+// K tile (four 32-key boxes per tile).  Barriers: bH0Full = "H0 ready", bSFull = "H1 ready", bH1Read.
+template <int kEmu, bool kAhead>
 __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kThreads, 1)
 attn_sm100_pair_kernel(const AttnParams p, const __grid_constant__ PairMaps maps) {
   extern __shared__ uint8_t smem_raw[];
@@ -144,6 +152,8 @@ attn_sm100_pair_kernel(const AttnParams p, const __grid_constant__ PairMaps maps
       ptx::mbar_init(bar(bSFull + g), 1);
       ptx::mbar_init(bar(bPReady + g), 8);       // one arrive per softmax warp of the group, both CTAs
       ptx::mbar_init(bar(bOFull + g), 1);
+      ptx::mbar_init(bar(bH1Read + g), 8);
+      ptx::mbar_init(bar(bH0Full + g), 1);
     }
     ptx::fence_barrier_init();
   }
@@ -171,8 +181,16 @@ attn_sm100_pair_kernel(const AttnParams p, const __grid_constant__ PairMaps maps
         const int row = k_start + tile_of(t >> 1) * kBN;
         const uint32_t dst = sRing + st * kItemBytes;
         if ((t & 1) == 0) {
-          for (int pnl = 0; pnl < 2; ++pnl)
-            ptx::tma_load_2d_pair(dst + pnl * kKPanel, &maps.k, bar(bFull + st), kvh * kD + pnl * 64, row + 64 * (int)rank);
+          if constexpr (kAhead) {
+            // [half h][panel][32 keys][128 B]: keys 64 h + 32 rank .. + 31 of the tile
+            for (int h = 0; h < 2; ++h)
+              for (int pnl = 0; pnl < 2; ++pnl)
+                ptx::tma_load_2d_pair(dst + h * kKPanel + pnl * (kKPanel / 2), &maps.k, bar(bFull + st),
+                                      kvh * kD + pnl * 64, row + 64 * h + 32 * (int)rank);
+          } else {
+            for (int pnl = 0; pnl < 2; ++pnl)
+              ptx::tma_load_2d_pair(dst + pnl * kKPanel, &maps.k, bar(bFull + st), kvh * kD + pnl * 64, row + 64 * (int)rank);
+          }
         } else {
           ptx::tma_load_2d_pair(dst, &maps.v, bar(bFull + st), kvh * kD + 64 * (int)rank, row);
         }
@@ -214,11 +232,76 @@ attn_sm100_pair_kernel(const AttnParams p, const __grid_constant__ PairMaps maps
                            acc || ks > 0);
       };
 
+      // kAhead: half h (64 keys) of S_g for tile j into column block (j & 1) ^ h
+      constexpr uint32_t kIdescS64 = ptx::instr_desc_bf16(256, 64, false);
+      auto issue_s_half = [&](int g, int st, int j, int h) {
+        const uint32_t d_tmem = tb + kColS + (uint32_t)(g * 128) + (uint32_t)((((j & 1) ^ h)) * 64);
+        const uint64_t qa = dQ + (uint64_t)((g * 2 * (kBM * 128)) >> 4);
+        const uint64_t kb = dK + (uint64_t)((st * kItemBytes + h * kKPanel) >> 4);
+#pragma unroll
+        for (int ks = 0; ks < 8; ++ks) {
+          const uint32_t qo = ((ks >> 2) * (kBM * 128) + (ks & 3) * 32) >> 4;
+          const uint32_t ko = ((ks >> 2) * (kKPanel / 2) + (ks & 3) * 32) >> 4;
+          ptx::mma_ss_pair(d_tmem, qa + qo, kb + ko, kIdescS64, ks > 0);
+        }
+      };
+      auto issue_pv_blk = [&](int g, int st, bool acc, int j) {     // P(j) sits in block j & 1
+        const uint32_t d_tmem = tb + kColO + (uint32_t)(g * 128);
+        const uint32_t a_tmem = tb + kColS + (uint32_t)(g * 128) + (uint32_t)((j & 1) * 64);
+        const uint64_t vb = dV + (uint64_t)((st * kItemBytes) >> 4);
+#pragma unroll
+        for (int ks = 0; ks < kBN / 16; ++ks)
+          ptx::mma_ts_pair(d_tmem, a_tmem + (uint32_t)(ks * 8), vb + (uint64_t)((ks * 2048) >> 4), kIdescO,
+                           acc || ks > 0);
+      };
+
       int st = 0, ph = 0;                               // ring position of the next item to consume
       auto advance = [&] { if (++st == kStages) { st = 0; ph ^= 1; } };
       ptx::mbar_wait_cluster(bar(bQFull), 0);
       ptx::mbar_wait_cluster(bar(bFull + 0), 0);        // K(0)
       ptx::tc_fence_after();
+      if constexpr (kAhead) {
+        if (ptx::elect_one()) {
+          for (int g = 0; g < 2; ++g) {
+            issue_s_half(g, 0, 0, 0); ptx::mma_commit_pair(bar(bH0Full + g));
+            issue_s_half(g, 0, 0, 1); ptx::mma_commit_pair(bar(bSFull + g));
+          }
+          ptx::mma_commit_pair(bar(bEmpty + 0));
+        }
+        __syncwarp();
+        advance();
+        for (int j = 0; j < ntot; ++j) {
+          const int vst = st, vph = ph;
+          advance();
+          const int kst = st, kph = ph;
+          const bool more = j + 1 < ntot;
+          if (more) advance();
+          ptx::mbar_wait_cluster(bar(bFull + vst), vph);
+#pragma unroll
+          for (int g = 0; g < 2; ++g) {
+            if (more) {
+              if (g == 0) ptx::mbar_wait_cluster(bar(bFull + kst), kph);
+              ptx::mbar_wait_cluster(bar(bH1Read + g), j & 1);       // H1(j)'s block has been read (both CTAs)
+              ptx::tc_fence_after();
+              if (ptx::elect_one()) { issue_s_half(g, kst, j + 1, 0); ptx::mma_commit_pair(bar(bH0Full + g)); }
+              __syncwarp();
+            }
+            ptx::mbar_wait_cluster(bar(bPReady + g), j & 1);
+            ptx::tc_fence_after();
+            if (ptx::elect_one()) {
+              issue_pv_blk(g, vst, j > 0, j);
+              if (!more) ptx::mma_commit_pair(bar(bOFull + g));
+              if (g == 1) ptx::mma_commit_pair(bar(bEmpty + vst));
+              if (more) {
+                issue_s_half(g, kst, j + 1, 1);                      // into P(j)'s block, behind PV(j)
+                ptx::mma_commit_pair(bar(bSFull + g));
+                if (g == 1) ptx::mma_commit_pair(bar(bEmpty + kst));
+              }
+            }
+            __syncwarp();
+          }
+        }
+      } else {
       if (ptx::elect_one()) {
         issue_s(0, 0); ptx::mma_commit_pair(bar(bSFull + 0));
         issue_s(1, 0); ptx::mma_commit_pair(bar(bSFull + 1));
@@ -254,6 +337,7 @@ attn_sm100_pair_kernel(const AttnParams p, const __grid_constant__ PairMaps maps
           }
         }
       }
+      }   // !kAhead
     }
   } else {
     // =========================== softmax groups (both CTAs) ===========================
@@ -270,13 +354,126 @@ attn_sm100_pair_kernel(const AttnParams p, const __grid_constant__ PairMaps maps
     const uint64_t sc2 = pk_f2(sc, sc);
 
     for (int j = 0; j < total; ++j) {
-      ptx::mbar_wait(bar(bSFull + g), j & 1);
+      if constexpr (kAhead) ptx::mbar_wait(bar(bH0Full + g), j & 1);          // first 64 keys of S(j)
+      else ptx::mbar_wait(bar(bSFull + g), j & 1);
       ptx::tc_fence_after();
       const int c0 = tile_of(j) * kBN;
       const bool full = bm_row == nullptr &&
                         tile_is_full(r0, r1, c0, c0 + kBN - 1, n, lrow, p.si, p.sl, p.mode);
       uint32_t pk[64];             // the row's 128 probabilities as bf16 pairs
       uint64_t sum2;               // two partial row sums
+      if constexpr (kAhead) {
+        // column blocks of this tile's two 64-key halves (they swap every tile); P goes to H0's
+        const uint32_t tH0 = tS + (uint32_t)((j & 1) * 64);
+        const uint32_t tH1 = tS + (uint32_t)(((j & 1) ^ 1) * 64);
+#pragma unroll 1
+        for (int attempt = 0;; ++attempt) {
+          const float neg_m = (m_ref == -INFINITY) ? 0.f : -m_ref;
+          const uint64_t negm2 = pk_f2(neg_m, neg_m);
+          float mx0 = -INFINITY, mx1 = -INFINITY;
+          sum2 = pk_f2(0.f, 0.f);
+          // A: raw scores of chunk c (in xr) -> t = x * scale - m_ref, in place; row max tracked
+          auto phase_a = [&](int c, uint32_t (&xr)[32]) {
+            float x[32];
+#pragma unroll
+            for (int e = 0; e < 32; ++e) x[e] = __uint_as_float(xr[e]);
+            if (!full) {
+              const int cb = c0 + c * 32;
+              const uint32_t bits = bm_row != nullptr ? bm_row[cb >> 5]
+                                                      : mask_word32(i, cb, n, lrow, p.si, p.sl, p.mode);
+#pragma unroll
+              for (int e = 0; e < 32; ++e) x[e] = ((bits >> e) & 1u) ? x[e] : -INFINITY;
+            }
+#pragma unroll
+            for (int e = 0; e < 32; e += 4) {
+              mx0 = fmaxf(mx0, fmaxf(x[e], x[e + 1]));
+              mx1 = fmaxf(mx1, fmaxf(x[e + 2], x[e + 3]));
+            }
+#pragma unroll
+            for (int e = 0; e < 32; e += 2) {
+              float a, b;
+              upk_f2(ffma2(pk_f2(x[e], x[e + 1]), sc2, negm2), a, b);
+              xr[e] = __float_as_uint(a);
+              xr[e + 1] = __float_as_uint(b);
+            }
+          };
+          // B: t of chunk c (in xr) -> probabilities, row sum, 16 packed bf16 pairs
+          auto phase_b = [&](int c, const uint32_t (&xr)[32]) {
+#pragma unroll
+            for (int e = 0; e < 32; e += 2) {
+              float a = __uint_as_float(xr[e]), b = __uint_as_float(xr[e + 1]);
+              uint64_t q2;
+              if ((e & 15) < kEmu) {
+                q2 = exp2_poly2(pk_f2(a, b));
+                upk_f2(q2, a, b);
+              } else {
+                a = fast_exp2(a);
+                b = fast_exp2(b);
+                q2 = pk_f2(a, b);
+              }
+              sum2 = fadd2(sum2, q2);
+              pk[c * 16 + e / 2] = pack2(a, b);
+            }
+          };
+          uint32_t b0[32], b1[32], b2[32];
+          ptx::tmem_ld32(tH0, b0);
+          ptx::tc_wait_ld();
+          ptx::tmem_ld32(tH0 + 32, b1);
+          phase_a(0, b0);
+          ptx::tc_wait_ld();
+          // everything that only needs H0 first (half of the pass), then wait for keys 64..127
+          phase_a(1, b1);
+          phase_b(0, b0);
+          phase_b(1, b1);
+          ptx::mbar_wait(bar(bSFull + g), j & 1);   // (completed long ago on a redo)
+          ptx::tc_fence_after();
+          ptx::tmem_ld32(tH1, b2);
+          ptx::tc_wait_ld();
+          ptx::tmem_ld32(tH1 + 32, b0);
+          phase_a(2, b2);
+          ptx::tc_wait_ld();
+          phase_a(3, b0);
+          phase_b(2, b2);
+          const float m_new = fmaxf(m_ref, fmaxf(mx0, mx1) * sc);
+          const bool grow = (m_new > m_ref + 8.0f) || (m_ref == -INFINITY && m_new > -INFINITY);
+          if (attempt == 1 || !__any_sync(0xffffffffu, grow)) {
+            // H1(j)'s block is read and will not be re-read: the leader may issue H0(j+1) into it
+            ptx::tc_fence_before();
+            __syncwarp();
+            if (lane == 0) ptx::mbar_arrive_leader(bar(bH1Read + g));
+            // the first half of P can go out while the last chunk is still being exponentiated
+            ptx::tmem_st32(tH0, *reinterpret_cast<uint32_t(*)[32]>(&pk[0]));
+            phase_b(3, b0);
+            break;
+          }
+          if (j > 0) {
+            const float alpha = (m_new == -INFINITY) ? 1.0f : fast_exp2(m_ref - m_new);
+            l_run *= alpha;
+#pragma unroll
+            for (int c = 0; c < 4; ++c) {
+              uint32_t r[32];
+              ptx::tmem_ld32(tO + c * 32, r);
+              ptx::tc_wait_ld();
+#pragma unroll
+              for (int e = 0; e < 32; ++e) r[e] = __float_as_uint(__uint_as_float(r[e]) * alpha);
+              ptx::tmem_st32(tO + c * 32, r);
+            }
+            ptx::tc_wait_st();
+          }
+          m_ref = m_new;
+        }
+        {
+          float a, b;
+          upk_f2(sum2, a, b);
+          l_run += a + b;
+        }
+        ptx::tmem_st32(tH0 + 32, *reinterpret_cast<uint32_t(*)[32]>(&pk[32]));
+        ptx::tc_wait_st();
+        ptx::tc_fence_before();
+        __syncwarp();
+        if (lane == 0) ptx::mbar_arrive_leader(bar(bPReady + g));
+        continue;
+      }
       // Optimistic single pass over S: exponentiate against the CURRENT reference max while tracking the
       // tile's max.  Only if some row's max outgrew the reference by more than 2^8 (always on the first
       // tile, rarely afterwards) the reference is refreshed, O and l are rescaled and the pass is redone
@@ -410,11 +607,26 @@ bool pair_supported(const AttnParams& p) {
 
 int launch_attn_sm100_pair(const AttnParams& p, cudaStream_t s) {
   if (!pair_supported(p)) return TMX_ERR_UNSUPPORTED;
-  auto kern = attn_sm100_pair_kernel<4>;
-  TMX_SET_SMEM_ATTR(kern, kAttrV3Pair, kSmem);
+  // Product: the look-ahead schedule with every exponential on MUFU (as in the single-CTA kernel).
+  using Kern = void (*)(const AttnParams, const PairMaps);
+  Kern kern = attn_sm100_pair_kernel<0, true>;
+  int slot = kAttrV3Pair;
+  bool ahead = true;
+#ifdef TMX_DEV
+  // TMX_SM100_VARIANT (developer build): 1 = look-ahead + 4/16 emulated exponentials, 2 = classic schedule
+  // (one N = 128 score MMA per tile) + 4/16, 3 = classic, all MUFU
+  switch (sm100_variant() & 3) {
+    case 1: kern = attn_sm100_pair_kernel<4, true>; slot = -1; break;
+    case 2: kern = attn_sm100_pair_kernel<4, false>; slot = -1; ahead = false; break;
+    case 3: kern = attn_sm100_pair_kernel<0, false>; slot = -1; ahead = false; break;
+    default: break;
+  }
+#endif
+  if (slot < 0) TMX_CUDA_TRY(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, kSmem));
+  else TMX_SET_SMEM_ATTR(kern, slot, kSmem);
   PairMaps maps;
   int st = tma_map_2d(&maps.q, p.q, p.total_T, (long long)p.Hq * kD, p.q_stride, kBM);
-  if (st == TMX_OK) st = tma_map_2d(&maps.k, p.k, p.total_kv, (long long)p.Hkv * kD, p.kv_stride, kBN / 2);
+  if (st == TMX_OK) st = tma_map_2d(&maps.k, p.k, p.total_kv, (long long)p.Hkv * kD, p.kv_stride, ahead ? kBN / 4 : kBN / 2);
   if (st == TMX_OK) st = tma_map_2d(&maps.v, p.v, p.total_kv, (long long)p.Hkv * kD, p.kv_stride, kBN);
   if (st != TMX_OK) return st;
   dim3 grid((unsigned)(2 * p.n_slots), (unsigned)(p.Hq / 4));     // clusters of 2 along x
