@@ -201,15 +201,19 @@ __device__ __forceinline__ void cluster_sync() {
 }
 // arrive on the barrier at the same offset in the LEADER CTA (from either CTA of the pair)
 __device__ __forceinline__ void mbar_arrive_leader(uint32_t bar) {
-  asm volatile("mbarrier.arrive.release.cluster.shared::cluster.b64 _, [%0];" ::"r"(bar & kPeerBitMask) : "memory");
+  // default (.release.cta) semantics, as CUTLASS' ClusterBarrier::arrive: the data handed over lives in TMEM
+  // and is ordered by tcgen05.fence::before/after_thread_sync; a .release.cluster here costs a MEMBAR.ALL.GPU
+  // per arrive in every softmax warp (measured: the pair kernel 12 % behind the single-CTA one)
+  asm volatile("mbarrier.arrive.shared::cluster.b64 _, [%0];" ::"r"(bar & kPeerBitMask) : "memory");
 }
-// wait with cluster-scope acquire (the arrivals may come from the peer CTA)
+// wait on a barrier whose arrivals may come from the peer CTA (plain acquire: see mbar_arrive_leader;
+// an .acquire.cluster wait adds a CCTL.IVALL L1 invalidation to every wait of the MMA issuer)
 __device__ __forceinline__ void mbar_wait_cluster(uint32_t bar, uint32_t parity) {
   uint32_t done = 0;
   for (uint32_t spins = 0; !done; ++spins) {
     asm volatile(
         "{\n.reg .pred p;\n"
-        "mbarrier.try_wait.parity.acquire.cluster.shared::cta.b64 p, [%1], %2;\n"
+        "mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n"
         "selp.u32 %0, 1, 0, p;\n}"
         : "=r"(done) : "r"(bar), "r"(parity) : "memory");
     if (!done && spins > (1u << 26)) __trap();
