@@ -41,6 +41,7 @@ def main():
     ap.add_argument("--kernels", nargs="+", default=["mma"])
     ap.add_argument("--modes", type=int, nargs="+", default=[1, 0])
     ap.add_argument("--params", type=int, nargs=3, default=[4, 32, 64])
+    ap.add_argument("--iters", type=int, default=0, help="timed iterations (default: 3 for long dense runs, else 10)")
     args = ap.parse_args()
     dev = "cuda:0"
     si, sl, last = args.params
@@ -52,7 +53,7 @@ def main():
         cu = torch.tensor([0, n], dtype=torch.int32, device=dev)
         for kern in args.kernels:
             for mode in args.modes:
-                it = 3 if (mode == 0 and n > 40000) else 10
+                it = args.iters or (3 if (mode == 0 and n > 40000) else 10)
                 ms = time_ms(lambda: ops.prefill_attn(q, k, v, cu, n, 128 ** -0.5, si, sl, last, mode, out=out, kernel=kern), 2, it)
                 p = pairs(n, si, sl, last, mode)
                 fl = 4 * 128 * args.hq * p

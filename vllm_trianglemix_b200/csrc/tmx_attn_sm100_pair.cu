@@ -607,19 +607,22 @@ bool pair_supported(const AttnParams& p) {
 
 int launch_attn_sm100_pair(const AttnParams& p, cudaStream_t s) {
   if (!pair_supported(p)) return TMX_ERR_UNSUPPORTED;
-  // Product: the look-ahead schedule with every exponential on MUFU (as in the single-CTA kernel).
+  // Product: the look-ahead schedule with 4 of every 16 exponentials on the FMA pipe (measured best under the
+  // power cap at 128K: 1178 vs 1155 TFLOP/s with all of them on MUFU; profiles/r02_pair_kernel.md).
   using Kern = void (*)(const AttnParams, const PairMaps);
-  Kern kern = attn_sm100_pair_kernel<0, true>;
+  Kern kern = attn_sm100_pair_kernel<4, true>;
   int slot = kAttrV3Pair;
   bool ahead = true;
 #ifdef TMX_DEV
-  // TMX_SM100_VARIANT (developer build): 1 = look-ahead + 4/16 emulated exponentials, 2 = classic schedule
-  // (one N = 128 score MMA per tile) + 4/16, 3 = classic, all MUFU
-  switch (sm100_variant() & 3) {
-    case 1: kern = attn_sm100_pair_kernel<4, true>; slot = -1; break;
-    case 2: kern = attn_sm100_pair_kernel<4, false>; slot = -1; ahead = false; break;
-    case 3: kern = attn_sm100_pair_kernel<0, false>; slot = -1; ahead = false; break;
-    default: break;
+  // TMX_SM100_VARIANT (developer build): bits 0-1 = exponentials on the FMA pipe per 16 (0, 4, 6, 8),
+  // bit 2 = classic schedule (one N = 128 score MMA per tile) instead of look-ahead
+  {
+    const int v = sm100_variant();
+    static const Kern ahead_k[4] = {attn_sm100_pair_kernel<0, true>, attn_sm100_pair_kernel<4, true>,
+                                    attn_sm100_pair_kernel<6, true>, attn_sm100_pair_kernel<8, true>};
+    static const Kern classic_k[4] = {attn_sm100_pair_kernel<0, false>, attn_sm100_pair_kernel<4, false>,
+                                      attn_sm100_pair_kernel<6, false>, attn_sm100_pair_kernel<8, false>};
+    if (v != 0) { ahead = (v & 4) == 0; kern = ahead ? ahead_k[v & 3] : classic_k[v & 3]; slot = -1; }
   }
 #endif
   if (slot < 0) TMX_CUDA_TRY(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, kSmem));
