@@ -366,33 +366,69 @@ attn_sm100_pair_kernel(const AttnParams p, const __grid_constant__ PairMaps maps
         // column blocks of this tile's two 64-key halves (they swap every tile); P goes to H0's
         const uint32_t tH0 = tS + (uint32_t)((j & 1) * 64);
         const uint32_t tH1 = tS + (uint32_t)(((j & 1) ^ 1) * 64);
+        auto masked = [&](int c, uint32_t (&xr)[32]) {          // apply the mask of chunk c (PARTIAL tiles only)
+          if (!full) {
+            const int cb = c0 + c * 32;
+            const uint32_t bits = bm_row != nullptr ? bm_row[cb >> 5]
+                                                    : mask_word32(i, cb, n, lrow, p.si, p.sl, p.mode);
+#pragma unroll
+            for (int e = 0; e < 32; ++e) xr[e] = ((bits >> e) & 1u) ? xr[e] : 0xff800000u;
+          }
+        };
+        // Refresh of the reference max: a separate sweep over the tile's 128 raw scores (still intact in
+        // TMEM: P is stored last), then O and l are rescaled.  Runs on the first tile, while a row has seen
+        // no unmasked score yet, and when the optimistic pass below overflows -- rarely.
+        auto refresh = [&]() {
+          ptx::mbar_wait(bar(bSFull + g), j & 1);
+          ptx::tc_fence_after();
+          float mx0 = -INFINITY, mx1 = -INFINITY;
+#pragma unroll
+          for (int c = 0; c < 4; ++c) {
+            uint32_t xr[32];
+            ptx::tmem_ld32((c < 2 ? tH0 : tH1) + (uint32_t)((c & 1) * 32), xr);
+            ptx::tc_wait_ld();
+            masked(c, xr);
+#pragma unroll
+            for (int e = 0; e < 32; e += 4) {
+              mx0 = fmaxf(mx0, fmaxf(__uint_as_float(xr[e]), __uint_as_float(xr[e + 1])));
+              mx1 = fmaxf(mx1, fmaxf(__uint_as_float(xr[e + 2]), __uint_as_float(xr[e + 3])));
+            }
+          }
+          const float m_new = fmaxf(m_ref, fmaxf(mx0, mx1) * sc);
+          if (j > 0) {
+            // S(j) complete => PV(j-1) complete (commit order); PV(j) waits for our arrive below
+            const float alpha = (m_new == -INFINITY) ? 1.0f : fast_exp2(m_ref - m_new);   // m_ref = -inf -> 0
+            l_run *= alpha;
+#pragma unroll
+            for (int c = 0; c < 4; ++c) {
+              uint32_t r[32];
+              ptx::tmem_ld32(tO + c * 32, r);
+              ptx::tc_wait_ld();
+#pragma unroll
+              for (int e = 0; e < 32; ++e) r[e] = __float_as_uint(__uint_as_float(r[e]) * alpha);
+              ptx::tmem_st32(tO + c * 32, r);
+            }
+            ptx::tc_wait_st();
+          }
+          m_ref = m_new;
+        };
+        if (__any_sync(0xffffffffu, m_ref == -INFINITY)) refresh();
+        // The optimistic pass: exponentiate against the CURRENT reference without looking for the row max at
+        // all (96 FMNMX per row and tile saved).  A stale reference shows up as large probabilities: the pass
+        // stands while the row sum of chunks 0-2 stays <= 2^8 and no score of chunk 3 exceeds the reference by
+        // 2^8 (checked where the old kernel knew its max: before H1's block is released and P is stored).
 #pragma unroll 1
         for (int attempt = 0;; ++attempt) {
           const float neg_m = (m_ref == -INFINITY) ? 0.f : -m_ref;
           const uint64_t negm2 = pk_f2(neg_m, neg_m);
-          float mx0 = -INFINITY, mx1 = -INFINITY;
           sum2 = pk_f2(0.f, 0.f);
-          // A: raw scores of chunk c (in xr) -> t = x * scale - m_ref, in place; row max tracked
+          // A: raw scores of chunk c (in xr) -> t = x * scale - m_ref, in place
           auto phase_a = [&](int c, uint32_t (&xr)[32]) {
-            float x[32];
-#pragma unroll
-            for (int e = 0; e < 32; ++e) x[e] = __uint_as_float(xr[e]);
-            if (!full) {
-              const int cb = c0 + c * 32;
-              const uint32_t bits = bm_row != nullptr ? bm_row[cb >> 5]
-                                                      : mask_word32(i, cb, n, lrow, p.si, p.sl, p.mode);
-#pragma unroll
-              for (int e = 0; e < 32; ++e) x[e] = ((bits >> e) & 1u) ? x[e] : -INFINITY;
-            }
-#pragma unroll
-            for (int e = 0; e < 32; e += 4) {
-              mx0 = fmaxf(mx0, fmaxf(x[e], x[e + 1]));
-              mx1 = fmaxf(mx1, fmaxf(x[e + 2], x[e + 3]));
-            }
+            masked(c, xr);
 #pragma unroll
             for (int e = 0; e < 32; e += 2) {
               float a, b;
-              upk_f2(ffma2(pk_f2(x[e], x[e + 1]), sc2, negm2), a, b);
+              upk_f2(ffma2(pk_f2(__uint_as_float(xr[e]), __uint_as_float(xr[e + 1])), sc2, negm2), a, b);
               xr[e] = __float_as_uint(a);
               xr[e + 1] = __float_as_uint(b);
             }
@@ -425,7 +461,7 @@ attn_sm100_pair_kernel(const AttnParams p, const __grid_constant__ PairMaps maps
           phase_a(1, b1);
           phase_b(0, b0);
           phase_b(1, b1);
-          ptx::mbar_wait(bar(bSFull + g), j & 1);   // (completed long ago on a redo)
+          ptx::mbar_wait(bar(bSFull + g), j & 1);   // (completed long ago after a refresh)
           ptx::tc_fence_after();
           ptx::tmem_ld32(tH1, b2);
           ptx::tc_wait_ld();
@@ -434,9 +470,18 @@ attn_sm100_pair_kernel(const AttnParams p, const __grid_constant__ PairMaps maps
           ptx::tc_wait_ld();
           phase_a(3, b0);
           phase_b(2, b2);
-          const float m_new = fmaxf(m_ref, fmaxf(mx0, mx1) * sc);
-          const bool grow = (m_new > m_ref + 8.0f) || (m_ref == -INFINITY && m_new > -INFINITY);
-          if (attempt == 1 || !__any_sync(0xffffffffu, grow)) {
+          bool stale = false;
+          if (attempt == 0) {
+            float sa, sb, t0 = -INFINITY, t1 = -INFINITY;
+            upk_f2(sum2, sa, sb);
+#pragma unroll
+            for (int e = 0; e < 32; e += 4) {
+              t0 = fmaxf(t0, fmaxf(__uint_as_float(b0[e]), __uint_as_float(b0[e + 1])));
+              t1 = fmaxf(t1, fmaxf(__uint_as_float(b0[e + 2]), __uint_as_float(b0[e + 3])));
+            }
+            stale = !(sa + sb <= 256.0f) || fmaxf(t0, t1) > 8.0f;        // (!(<=) also catches NaN / inf)
+          }
+          if (!__any_sync(0xffffffffu, stale)) {
             // H1(j)'s block is read and will not be re-read: the leader may issue H0(j+1) into it
             ptx::tc_fence_before();
             __syncwarp();
@@ -446,21 +491,7 @@ attn_sm100_pair_kernel(const AttnParams p, const __grid_constant__ PairMaps maps
             phase_b(3, b0);
             break;
           }
-          if (j > 0) {
-            const float alpha = (m_new == -INFINITY) ? 1.0f : fast_exp2(m_ref - m_new);
-            l_run *= alpha;
-#pragma unroll
-            for (int c = 0; c < 4; ++c) {
-              uint32_t r[32];
-              ptx::tmem_ld32(tO + c * 32, r);
-              ptx::tc_wait_ld();
-#pragma unroll
-              for (int e = 0; e < 32; ++e) r[e] = __float_as_uint(__uint_as_float(r[e]) * alpha);
-              ptx::tmem_st32(tO + c * 32, r);
-            }
-            ptx::tc_wait_st();
-          }
-          m_ref = m_new;
+          refresh();
         }
         {
           float a, b;
@@ -474,10 +505,6 @@ attn_sm100_pair_kernel(const AttnParams p, const __grid_constant__ PairMaps maps
         if (lane == 0) ptx::mbar_arrive_leader(bar(bPReady + g));
         continue;
       }
-      // Optimistic single pass over S: exponentiate against the CURRENT reference max while tracking the
-      // tile's max.  Only if some row's max outgrew the reference by more than 2^8 (always on the first
-      // tile, rarely afterwards) the reference is refreshed, O and l are rescaled and the pass is redone
-      // -- S is still intact in TMEM because P is stored last.
 #pragma unroll 1
       for (int attempt = 0;; ++attempt) {
         const float neg_m = (m_ref == -INFINITY) ? 0.f : -m_ref;
