@@ -105,7 +105,7 @@ struct Plan {
 
 // How a call is served.  AUTO picks tcgen05 wherever two query heads share a KV head and the
 // scale is positive (the tcgen05 kernels take the row max on raw scores):
-//   dense-causal / unmasked   attn_sm100_v3_kernel over the block index
+//   dense-causal / unmasked   attn_sm100_pair_kernel (GQA ratio % 4 == 0) or attn_sm100_v3_kernel over the block index
 //   triangle, sink < 16 and window <= 112 keys (the reference defaults)
 //                             attn_stream3_kernel (HBM-bound pass) + split-KV tail on tcgen05
 //   any other triangle        attn_sm100_v3_kernel over the block index (rows before the dense
@@ -113,14 +113,20 @@ struct Plan {
 // mma.sync serves odd GQA ratios, non-positive scales and explicit kernel="mma" (the cross-check).
 // `ctx`: the call carries context keys (chunked prefill / decode): block-index kernels only.
 Plan make_plan(int B, int total_T, int max_seqlen, int Hq, int Hkv, int si, int sl, int last, int mode,
-               int kernel, bool has_bitmask, bool scale_pos, bool ctx) {
+               int kernel, bool has_bitmask, bool scale_pos, bool ctx, bool paged = false) {
   Plan pl{};
   const bool pairable = Hkv > 0 && Hq % Hkv == 0 && (Hq / Hkv) % 2 == 0;
   pl.kernel = kernel;
   // explicit request for the CTA-pair kernel (AUTO's choice between the two tcgen05 kernels: see below)
   pl.pair = kernel == TMX_KERNEL_TCGEN05_PAIR;
   if (pl.pair) pl.kernel = kernel = TMX_KERNEL_TCGEN05;
-  if (kernel == TMX_KERNEL_AUTO) pl.kernel = (pairable && scale_pos) ? TMX_KERNEL_TCGEN05 : TMX_KERNEL_MMA;
+  if (kernel == TMX_KERNEL_AUTO) {
+    pl.kernel = (pairable && scale_pos) ? TMX_KERNEL_TCGEN05 : TMX_KERNEL_MMA;
+    // block-index pass: CTA pairs (cta_group::2) wherever four query heads share a KV head -- +6 % on the
+    // 128K dense layer over the single-CTA kernel (profiles/r02_pair_kernel.md); paged K/V stay on the
+    // single-CTA kernel (one TMA box per page)
+    pl.pair = pl.kernel == TMX_KERNEL_TCGEN05 && (Hq / Hkv) % 4 == 0 && !paged;
+  }
   const bool tri = mode == TMX_MODE_TRIANGLE;
   pl.bn = 64;
   pl.bm = tri ? 64 : 128;
@@ -317,7 +323,8 @@ extern "C" int tmx_chunked_prefill_attn(void* out, const void* q, const int32_t*
   const float scale_log2 = scale * 1.4426950408889634f;
   const bool scale_pos = scale_log2 > 0.f;
   if (kernel >= TMX_KERNEL_TCGEN05 && !scale_pos) return TMX_ERR_UNSUPPORTED;
-  Plan pl = make_plan(B, total_Tq, max_query_len, Hq, Hkv, si, sl, last, mode, kernel, false, scale_pos, true);
+  Plan pl = make_plan(B, total_Tq, max_query_len, Hq, Hkv, si, sl, last, mode, kernel, false, scale_pos, true,
+                      block_table != nullptr);
   if (!workspace || workspace_bytes < pl.total || misaligned(workspace)) return TMX_ERR_WORKSPACE;
 
   AttnParams p{};
