@@ -29,22 +29,47 @@ ROOT = os.path.dirname(os.path.abspath(__file__))
 if ROOT not in sys.path:
     sys.path.insert(0, ROOT)
 
-SEQ_LEN = 131072
-NUM_LAYERS = 36
-HQ, HKV, D = 32, 8, 128
 SI, SL, LAST = 4, 32, 64                       # reference defaults (trianglemix_attention.py:16-18)
-TRIANGLE_LAYERS = list(range(28, 36))          # for_qwen3("8B") -> 8 triangle layers, placed deep
-METRIC = "qwen3_8b_128k_trianglemix_prefill_attn_tokens_per_s"
+D = 128
 UNIT = "tokens/s"
+# BASELINE.json configs (0-based).  2 is the metric's configuration (the driver's line); 3 and 4 are the
+# multi-GPU configurations, run with --config 3|4 (profiles/r02_scale_config{3,4}.json).
+CONFIGS = {
+    2: dict(name="BASELINE configs[2]: Qwen3-8B 36-layer prefill attention, 128K tokens, 28 dense-causal shallow "
+                 "layers + 8 triangle deep layers (si=4, sl=32, last=64)",
+            metric="qwen3_8b_128k_trianglemix_prefill_attn_tokens_per_s",
+            seq_lens=[131072], layers=36, triangle=list(range(28, 36)), hq=32, hkv=8),   # for_qwen3("8B") -> 8
+    3: dict(name="BASELINE configs[3]: Qwen3-32B (64 q / 8 kv heads) 64-layer prefill attention, 128K tokens, "
+                 "52 dense-causal shallow layers + 12 triangle deep layers (for_qwen3('32B')), head-sharded",
+            metric="qwen3_32b_128k_trianglemix_prefill_attn_tokens_per_s",
+            seq_lens=[131072], layers=64, triangle=list(range(52, 64)), hq=64, hkv=8),
+    4: dict(name="BASELINE configs[4]: batched varlen prefill, 8 sequences 8K-64K (249,856 tokens), Qwen3-8B shape, "
+                 "36 layers (28 dense-causal + 8 triangle deep), head-sharded",
+            metric="qwen3_8b_varlen8_trianglemix_prefill_attn_tokens_per_s",
+            seq_lens=[8192, 12288, 16384, 24576, 32768, 40960, 49152, 65536], layers=36,
+            triangle=list(range(28, 36)), hq=32, hkv=8),
+}
+CFG = dict(CONFIGS[2])
+SEQ_LEN, NUM_LAYERS, HQ, HKV = sum(CFG["seq_lens"]), CFG["layers"], CFG["hq"], CFG["hkv"]
+TRIANGLE_LAYERS = CFG["triangle"]
+METRIC = CFG["metric"]
+
+
+def select_config(idx, seq_len=None):
+    global CFG, SEQ_LEN, NUM_LAYERS, HQ, HKV, TRIANGLE_LAYERS, METRIC
+    CFG = dict(CONFIGS[idx])
+    if seq_len is not None and len(CFG["seq_lens"]) == 1:
+        CFG["seq_lens"] = [seq_len]
+    SEQ_LEN, NUM_LAYERS, HQ, HKV = sum(CFG["seq_lens"]), CFG["layers"], CFG["hq"], CFG["hkv"]
+    TRIANGLE_LAYERS, METRIC = CFG["triangle"], CFG["metric"]
 
 
 def workload_config(n_gpus):
-    return {"workload": "BASELINE configs[2]: Qwen3-8B 36-layer prefill attention, 128K tokens, "
-                        "28 dense-causal shallow layers + 8 triangle deep layers (si=4, sl=32, last=64)",
-            "seq_len": SEQ_LEN, "layers": NUM_LAYERS, "triangle_layers": TRIANGLE_LAYERS,
-            "q_heads": HQ, "kv_heads": HKV, "head_dim": D,
+    qkv_gb = 2.0 * SEQ_LEN * D * (HQ + 2 * HKV) / 1e9
+    return {"workload": CFG["name"], "seq_len": SEQ_LEN, "seq_lens": CFG["seq_lens"], "layers": NUM_LAYERS,
+            "triangle_layers": TRIANGLE_LAYERS, "q_heads": HQ, "kv_heads": HKV, "head_dim": D,
             "parallelism": "heads/%d" % n_gpus if n_gpus > 1 else "single",
-            "l2_policy": "inputs (1.6 GB q/k/v) larger than the 126 MB L2; no explicit flush"}
+            "l2_policy": "inputs (%.1f GB q/k/v over all ranks) larger than the 126 MB L2; no explicit flush" % qkv_gb}
 
 
 def load_peaks():
@@ -137,6 +162,70 @@ def cpu_reference_sample(rows_per_layer_type, threads):
     return 1.0 / per_tok, out
 
 
+REF_DIR = os.path.join(ROOT, "baseline", "_ref")     # `pip install --target baseline/_ref` of the unmodified reference
+
+
+def reference_measured(threads, sizes=(2048, 4096)):
+    """The UNMODIFIED reference, loaded by path from baseline/_ref (the offline pip install of /root/reference;
+    nothing here reads /root/reference): BASELINE configs[0] -- Qwen3-0.6B attention shape (16 q / 8 kv heads
+    repeated to 16, head_dim 128), batch 1, seq 2048 -- mask generation by
+    TriangleMixMaskGenerator.get_attention_mask(use_triangle=True) (vllm/attention/trianglemix_attention.py:221-261,
+    its own Python loops) + AscendTriangleMixAttention.forward with that mask (vllm/attention/ascend_trianglemix.py:
+    52-108), fp32, all host threads; and the same at 4096 tokens.  Real loops, real op, measured end to end.
+    Returns None when the install is absent."""
+    base = os.path.join(REF_DIR, "vllm", "attention")
+    if not os.path.exists(os.path.join(base, "trianglemix_attention.py")):
+        return None
+    import importlib.util
+    import types
+    import torch
+    saved = {k: sys.modules.get(k) for k in ("vllm", "vllm.attention")}
+    try:
+        for name in ("vllm", "vllm.attention"):
+            m = types.ModuleType(name)
+            m.__path__ = []
+            sys.modules[name] = m
+        mods = {}
+        for short in ("trianglemix_attention", "ascend_trianglemix"):
+            full = "vllm.attention." + short
+            spec = importlib.util.spec_from_file_location(full, os.path.join(base, short + ".py"))
+            mod = importlib.util.module_from_spec(spec)
+            sys.modules[full] = mod
+            spec.loader.exec_module(mod)
+            mods[short] = mod
+        tma, asc = mods["trianglemix_attention"], mods["ascend_trianglemix"]
+        torch.set_num_threads(threads)
+        out = []
+        for n in sizes:
+            g = torch.Generator().manual_seed(0)
+            hq, hkv = 16, 8
+            q = torch.randn(1, n, hq, D, generator=g).bfloat16().float()
+            k = torch.randn(1, n, hkv, D, generator=g).bfloat16().float().repeat_interleave(hq // hkv, dim=2)
+            v = torch.randn(1, n, hkv, D, generator=g).bfloat16().float().repeat_interleave(hq // hkv, dim=2)
+            cfg = tma.TriangleMixConfig(num_sink_tokens=SI, sliding_window_size=SL, num_last_tokens=LAST)
+            gen = tma.TriangleMixMaskGenerator(cfg)
+            t0 = time.perf_counter()
+            mask = gen.get_attention_mask(n, 0, torch.device("cpu"), torch.float32, use_triangle=True)
+            t1 = time.perf_counter()
+            op = asc.AscendTriangleMixAttention(num_heads=hq, head_dim=D, scale=D ** -0.5)
+            o = op.forward(q, k, v, attn_mask=mask)
+            t2 = time.perf_counter()
+            out.append({"seq_len": n, "mask_s": t1 - t0, "attention_s": t2 - t1, "layer_s": t2 - t0,
+                        "tokens_per_s_one_layer": n / (t2 - t0), "checksum": float(o.double().sum())})
+        return {"kind": "reference", "source": "baseline/_ref (pip install --target of the unmodified reference)",
+                "cores": threads, "shape": "B1, 16 q heads (8 kv heads repeated), head_dim 128, fp32, triangle mask "
+                "si=4 sl=32 last=64; ONE layer: get_attention_mask + AscendTriangleMixAttention.forward",
+                "points": out}
+    finally:
+        for k, v in saved.items():
+            if v is None:
+                sys.modules.pop(k, None)
+            else:
+                sys.modules[k] = v
+        for short in ("trianglemix_attention", "ascend_trianglemix"):
+            sys.modules.pop("vllm.attention." + short, None)
+
+
 def run_reference_arm(args, rank):
     if rank != 0:
         return
@@ -151,6 +240,7 @@ def run_reference_arm(args, rank):
             break
     timed = vals[args.warmup:] or vals[-1:]
     tok_s = sum(x[0] for x in timed) / len(timed)
+    measured = reference_measured(threads)
     sample = ("%d query rows spread over the 128K prompt x all 131072 keys x 32 heads, one triangle layer "
               "(mask rows by the reference's scalar Python loops) + one dense layer (tril rows), fp32; "
               "scaled to 36 layers (8 triangle + 28 dense)" % rows)
@@ -158,7 +248,8 @@ def run_reference_arm(args, rank):
             "steps": len(timed), "warmup": args.warmup, "ms_per_step": SEQ_LEN / tok_s * 1e3,
             "higher_is_better": True, "scaling": "strong", "vs_baseline": None, "dtype": "f32",
             "data": "synthetic", "config": workload_config(args.gpus),
-            "cpu_baseline": {"value": tok_s, "unit": UNIT, "cores": threads, "kind": "port", "sample": sample},
+            "cpu_baseline": {"value": tok_s, "unit": UNIT, "cores": threads, "kind": "port", "sample": sample,
+                             "measured": measured},
             "e2e": {"value": tok_s, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
             "gpu_launches": 0, "detail": detail}
     print(json.dumps(line), flush=True)
@@ -170,10 +261,13 @@ def main():
     ap.add_argument("--steps", type=int, default=2)
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
-    ap.add_argument("--kernel", default="auto", choices=["auto", "mma", "tcgen05"])
-    ap.add_argument("--seq-len", type=int, default=SEQ_LEN, help="developer override (invalidates the metric)")
+    ap.add_argument("--kernel", default="auto", choices=["auto", "mma", "tcgen05", "pair"])
+    ap.add_argument("--config", type=int, default=2, choices=sorted(CONFIGS),
+                    help="BASELINE.json configs index: 2 = the metric (default), 3 = Qwen3-32B heads, 4 = 8-sequence varlen")
+    ap.add_argument("--seq-len", type=int, default=None, help="developer override (invalidates the metric)")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     args = ap.parse_args()
+    select_config(args.config, args.seq_len)
     rank = int(os.environ.get("RANK", "0"))
     world = int(os.environ.get("WORLD_SIZE", "1"))
     local = int(os.environ.get("LOCAL_RANK", "0"))
@@ -196,7 +290,7 @@ def main():
             os.environ["NCCL_DEBUG"] = "WARN"
         os.environ.setdefault("NCCL_DEBUG_FILE", "/dev/stderr")
         dist.init_process_group("nccl", device_id=dev)
-    n = args.seq_len
+    n = SEQ_LEN
     assert HKV % world == 0, "head sharding needs kv_heads % n_gpus == 0"
     hq, hkv = HQ // world, HKV // world
 
@@ -225,10 +319,10 @@ def main():
     scale = D ** -0.5
     layers = [tmx.TriangleMixImpl(hq, D, scale, num_kv_heads=hkv, trianglemix_config=cfg, layer_idx=i,
                                   num_layers=NUM_LAYERS, kernel=args.kernel) for i in range(NUM_LAYERS)]
-    meta = tmx.TriangleMixMetadataBuilder.from_seq_lens([n], dev)
+    meta = tmx.TriangleMixMetadataBuilder.from_seq_lens(CFG["seq_lens"], dev)
     launches = [0]
 
-    def step(qd, kd, vd, events=None):
+    def step(qd, kd, vd, events=None, gather=True):
         for i, impl in enumerate(layers):
             o = out if og is None else og.buffer(i)
             if events is not None:
@@ -237,9 +331,9 @@ def main():
             launches[0] += ops.last_launch_count()
             if events is not None:
                 events[i][1].record()
-            if og is not None:     # output all-gather of this layer's [T, Hq/P, D] shard, asynchronous
+            if og is not None and gather:     # output all-gather of this layer's [T, Hq/P, D] shard, asynchronous
                 og.launch(i)
-        if og is not None:
+        if og is not None and gather:
             og.finish()
         return o
 
@@ -276,6 +370,19 @@ def main():
                 if i not in TRIANGLE_LAYERS]
     tri_ms = [ev[s][i][0].elapsed_time(ev[s][i][1]) for s in range(args.steps) for i in TRIANGLE_LAYERS]
     dense_avg, tri_avg = sum(dense_ms) / len(dense_ms), sum(tri_ms) / len(tri_ms)
+
+    # ---- the same step without the output all-gather (report both) -----------------------
+    no_gather_ms = None
+    if world > 1:
+        barrier()
+        t0.record()
+        for _ in range(args.steps):
+            step(q, k, v, gather=False)
+        t1.record()
+        barrier()
+        ms3 = torch.tensor([t0.elapsed_time(t1)], device=dev)
+        dist.all_reduce(ms3, op=dist.ReduceOp.MAX)
+        no_gather_ms = float(ms3.item()) / args.steps
 
     # ---- end to end through host buffers ------------------------------------------------
     def e2e_step():
@@ -331,7 +438,7 @@ def main():
         if prologue is not None and peaks.get("hbm_gbs"):
             prologue["peak"] = peaks["hbm_gbs"]
             prologue["frac"] = prologue["achieved"] / peaks["hbm_gbs"]
-        pairs_dense = n * (n + 1) // 2
+        pairs_dense = sum(x * (x + 1) // 2 for x in CFG["seq_lens"])
         flops_dense = 4.0 * D * hq * pairs_dense
         achieved = flops_dense / (dense_avg * 1e-3) / 1e12
         traffic = None
@@ -349,16 +456,23 @@ def main():
                         "h2d_bytes_per_step": (q_host.numel() + k_host.numel() + v_host.numel()) * 2,
                         "d2h_bytes_per_step": out_host.numel() * 2, "ms_per_step": e2e_ms},
                 "gpu_launches": n_launch,
+                "all_gather": None if world == 1 else {
+                    "ms_per_step_with": ms_per_step, "ms_per_step_without": no_gather_ms,
+                    "exposed_ms_per_step": ms_per_step - no_gather_ms,
+                    "bytes_per_rank_per_layer": n * hq * D * 2,
+                    "how": "NCCL all_gather_into_tensor of each layer's [T, Hq/P, D] output shard, asynchronous, "
+                           "double-buffered (head_shard.OverlappedGather)"},
                 "prologue": prologue,
                 "roofline": {"bound": "tensor", "kernel": "dense-causal attention layer (per rank)",
                              "achieved": achieved, "peak": peaks["tflops"], "unit": "TFLOP/s",
                              "frac": achieved / peaks["tflops"], "traffic": traffic,
                              "peak_source": peaks["source"],
                              "algorithmic_flops_per_launch": flops_dense, "avg_launch_ms": dense_avg}}
-        if world == 1 and not args.no_cpu_baseline:
+        if world == 1 and not args.no_cpu_baseline and args.config == 2:
             threads = os.cpu_count() or 1
             tok_s, detail = cpu_reference_sample(8, threads)
             line["cpu_baseline"] = {
+                "measured": reference_measured(threads),
                 "value": tok_s, "unit": UNIT, "cores": threads, "kind": "port",
                 "sample": "8 query rows x 131072 keys x 32 heads for one triangle + one dense layer "
                           "(reference's Python mask loops + fp32 eager attention), scaled to 36 layers",
