@@ -201,11 +201,7 @@ class TriangleMixImpl:
                     "this batch carries context keys (seq_lens != query lengths: chunked prefill, a prefix-cache "
                     "hit or a decode step) but no kv_cache / block_table / seq_lens to read them from")
             key_cache, value_cache = kv_cache.unbind(0)
-            ops.chunked_prefill_attn(q, attn_metadata.query_start_loc, attn_metadata.seq_lens,
-                                     attn_metadata.max_query_len, self.scale, si, sl, last,
-                                     self._context_mode(mode, attn_metadata), key_cache=key_cache,
-                                     value_cache=value_cache, block_table=attn_metadata.block_table, out=out,
-                                     kernel=self.kernel)
+            self._context_prefill(q, out, key_cache, value_cache, attn_metadata, mode, si, sl, last)
             return output
         self._whole_sequence_prefill(q, k, v, out, attn_metadata, mode, si, sl, last)
         return output
@@ -214,15 +210,35 @@ class TriangleMixImpl:
     # sequence runs on the stock causal backend even in a triangle layer.
     SHORT_SEQ_DENSE = 2048
 
-    def _context_mode(self, mode: int, md: TriangleMixMetadata) -> int:
-        if mode != ops.TRIANGLE:
-            return mode
-        if md.max_seq_len <= self.SHORT_SEQ_DENSE:
-            return ops.DENSE_CAUSAL
-        if md.seq_lens_cpu is not None and bool((md.seq_lens_cpu <= self.SHORT_SEQ_DENSE).any()):
-            raise NotImplementedError("a chunked batch mixing sequences <= 2048 (dense by the reference's threshold) "
-                                      "and > 2048 tokens in a triangle layer: schedule them in separate steps")
-        return mode
+    def _context_prefill(self, q, out, key_cache, value_cache, md: TriangleMixMetadata, mode, si, sl, last) -> None:
+        """Keys from the paged cache.  In a triangle layer a sequence of <= 2048 tokens (so far) is dense-causal
+        (the reference's threshold); runs of consecutive sequences of one class go out as one kernel call."""
+        def call(b0, b1, t0, t1, qmax, m):
+            whole = b0 == 0 and b1 == md.seq_lens.numel()
+            cu = md.query_start_loc if whole else (md.query_start_loc[b0:b1 + 1] - md.query_start_loc[b0]).contiguous()
+            ops.chunked_prefill_attn(q[t0:t1], cu, md.seq_lens[b0:b1], qmax, self.scale, si, sl, last, m,
+                                     key_cache=key_cache, value_cache=value_cache, block_table=md.block_table[b0:b1],
+                                     out=out[t0:t1], kernel=self.kernel)
+
+        nseq = md.seq_lens.numel()
+        if mode != ops.TRIANGLE or md.max_seq_len <= self.SHORT_SEQ_DENSE:
+            call(0, nseq, 0, md.num_actual_tokens, md.max_query_len, ops.DENSE_CAUSAL if mode == ops.TRIANGLE else mode)
+            return
+        if md.seq_lens_cpu is None or md.query_start_loc_cpu is None:
+            raise NotImplementedError("a triangle layer needs the CPU copies of seq_lens / query_start_loc to separate "
+                                      "sequences <= 2048 tokens (dense by the reference's threshold) from longer ones")
+        lens = md.seq_lens_cpu[:nseq].tolist()
+        starts = md.query_start_loc_cpu[:nseq + 1].tolist()
+        b0 = 0
+        while b0 < nseq:
+            short = lens[b0] <= self.SHORT_SEQ_DENSE
+            b1 = b0
+            while b1 < nseq and (lens[b1] <= self.SHORT_SEQ_DENSE) == short:
+                b1 += 1
+            if starts[b1] > starts[b0]:
+                qmax = max(starts[b + 1] - starts[b] for b in range(b0, b1))
+                call(b0, b1, starts[b0], starts[b1], qmax, ops.DENSE_CAUSAL if short else ops.TRIANGLE)
+            b0 = b1
 
     def _whole_sequence_prefill(self, q, k, v, out, md: TriangleMixMetadata, mode, si, sl, last) -> None:
         cu, cu_cpu = md.query_start_loc, md.query_start_loc_cpu
