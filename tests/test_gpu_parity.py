@@ -317,3 +317,31 @@ def test_attention_fuzz_vs_oracle(ops, seed):
     out = ops.prefill_attn(q.to(DEV), k.to(DEV), v.to(DEV), cu, max(lens), scale, si, sl, last, mode, kernel=kernel)
     ref = orc.attention_varlen_fp32(q, k, v, cu_list, scale, si, sl, last, mode)
     _check(out.cpu(), ref, (seed, lens, hq, hkv, si, sl, last, mode, kernel))
+
+
+# ------------------------------------------------------------------ torch.library boundary
+def test_registered_torch_op_matches_ctypes_path(ops):
+    """torch.ops.trianglemix.prefill_attn (TORCH_LIBRARY TU) and the ctypes binding call the same entry point."""
+    from vllm_trianglemix_b200 import torch_ops
+    n, hq, hkv = 3000, 8, 2
+    q, k, v = _rand(n, hq, hkv, seed=21)
+    qd, kd, vd = q.to(DEV), k.to(DEV), v.to(DEV)
+    cu = torch.tensor([0, n], dtype=torch.int32, device=DEV)
+    for mode in (ops.TRIANGLE, ops.DENSE_CAUSAL):
+        a = ops.prefill_attn(qd, kd, vd, cu, n, 0.088, 4, 32, 64, mode)
+        b = torch_ops.prefill_attn(qd, kd, vd, cu, n, 0.088, 4, 32, 64, mode)
+        assert torch.equal(a, b)
+    t = torch_ops.load()
+    bits = torch.empty((n, ops.bitmask_stride_words(n)), dtype=torch.int32, device=DEV)
+    t.mask_bits(bits, n, 4, 32, 64, ops.PIECES["triangle"])
+    assert torch.equal(bits, ops.mask_bits(n, 4, 32, 64, "triangle", DEV))
+    # the op is traceable: torch.compile sees a registered, mutating op instead of an opaque ctypes call
+    ws = torch.empty(t.attn_workspace_bytes(1, n, n, hq, hkv, 128, 4, 32, 64, 1, 0), dtype=torch.uint8, device=DEV)
+
+    def f(qq, kk, vv):
+        o = torch.empty_like(qq)
+        torch.ops.trianglemix.prefill_attn(o, qq, kk, vv, cu, n, 0.088, 4, 32, 64, 1, None, None, ws, 0)
+        return o * 1.0
+
+    c = torch.compile(f, fullgraph=True, backend="eager")(qd, kd, vd)
+    assert torch.equal(c, ops.prefill_attn(qd, kd, vd, cu, n, 0.088, 4, 32, 64, ops.TRIANGLE))

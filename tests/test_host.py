@@ -50,6 +50,26 @@ def test_ctypes_table_matches_header():
     assert sorted(_lib.SIGNATURES) == _declared_symbols()
 
 
+def test_torch_library_ops_are_registered():
+    """The TORCH_LIBRARY TU loads without a GPU and registers every op with a mutating schema."""
+    from vllm_trianglemix_b200 import torch_ops
+    t = torch_ops.load()
+    for name in ("prefill_attn", "chunked_prefill_attn", "qk_norm_rope", "reshape_and_cache_flash", "mask_bits",
+                 "mask_additive", "attn_workspace_bytes"):
+        assert hasattr(t, name), name
+    schema = str(torch.ops.trianglemix.prefill_attn.default._schema)
+    assert "Tensor(a!) out" in schema and "Tensor? bitmask" in schema
+    # host-only op: same number as the C ABI
+    lib = _lib.load()
+    assert t.attn_workspace_bytes(1, 4096, 4096, 32, 8, 128, 4, 32, 64, 1, 0) == \
+        lib.tmx_attn_workspace_bytes(1, 4096, 4096, 32, 8, 128, 4, 32, 64, 1, 0)
+    # CPU tensors are refused by the op itself
+    x = torch.zeros(4, 2, 128, dtype=torch.bfloat16)
+    with pytest.raises((RuntimeError, NotImplementedError)):
+        t.prefill_attn(x, x, x, x, torch.tensor([0, 4], dtype=torch.int32), 4, 0.1, 4, 32, 64, 1, None, None,
+                       torch.zeros(256, dtype=torch.uint8), 0)
+
+
 def test_status_strings_and_version():
     lib = _lib.load()
     assert lib.tmx_version() >= 100
