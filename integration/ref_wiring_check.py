@@ -20,7 +20,16 @@ import sys
 ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 sys.path.insert(1, ROOT)          # after the reference root, before site-packages
 
+import types  # noqa: E402
+
 import torch  # noqa: E402
+
+if "--gpu" in sys.argv:
+    # On a GPU box the reference selects its CUDA platform, whose module starts with a bare `import vllm._C`
+    # (vllm/platforms/cuda.py:18) -- the compiled extension, which the `VLLM_TARGET_DEVICE=empty` install does not
+    # contain.  Nothing on this path calls into it (our backend replaces the kernels), so an empty stand-in
+    # module lets the unmodified Python of the reference load.
+    sys.modules.setdefault("vllm._C", types.ModuleType("vllm._C"))
 import vllm  # noqa: E402
 from vllm.attention.layer import Attention  # noqa: E402
 from vllm.config import CacheConfig, DeviceConfig, VllmConfig, set_current_vllm_config  # noqa: E402
