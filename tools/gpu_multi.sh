@@ -10,7 +10,7 @@ for stage in "$@"; do
   echo "=== P=$P stage $name $arg"
   case $name in
     check)
-      timeout 900 $RUN --master-port 29511 tools/multi_gpu_check.py --n ${arg:-131072} --out gpurun_out/multi_gpu_check_n$P.json \
+      timeout 900 $RUN --master-port 29511 tools/multi_gpu_check.py --tokens ${arg:-131072} --out gpurun_out/multi_gpu_check_n$P.json \
         > gpurun_out/multi_gpu_check_n$P.log 2>&1; echo "check rc=$?"
       grep -v "^W\|^\[W" gpurun_out/multi_gpu_check_n$P.log | tail -6 ;;
     bench)

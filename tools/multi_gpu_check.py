@@ -23,7 +23,7 @@ from vllm_trianglemix_b200 import head_shard
 
 def main():
     ap = argparse.ArgumentParser()
-    ap.add_argument("--n", type=int, default=32768)
+    ap.add_argument("--tokens", dest="n", type=int, default=32768)
     ap.add_argument("--out", default=None)
     args = ap.parse_args()
     rank, world, local = (int(os.environ[k]) for k in ("RANK", "WORLD_SIZE", "LOCAL_RANK"))
