@@ -266,6 +266,8 @@ def main():
                     help="BASELINE.json configs index: 2 = the metric (default), 3 = Qwen3-32B heads, 4 = 8-sequence varlen")
     ap.add_argument("--seq-len", type=int, default=None, help="developer override (invalidates the metric)")
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--gather", default="peer", choices=["peer", "nccl"],
+                    help="output all-gather at N > 1: NVLink peer-memory push (default; falls back to NCCL) or ncclAllGather")
     args = ap.parse_args()
     select_config(args.config, args.seq_len)
     rank = int(os.environ.get("RANK", "0"))
@@ -312,7 +314,8 @@ def main():
     # two output / gather buffers: the all-gather of layer L runs on NCCL's stream while layer L+1
     # computes into the other buffer ("overlap with the next layer's attention")
     from vllm_trianglemix_b200 import head_shard
-    og = head_shard.OverlappedGather((n, hq * D), torch.bfloat16, dev, depth=2) if world > 1 else None
+    og, gather_kind = head_shard.make_gather(args.gather, (n, hq * D), torch.bfloat16, dev, depth=2) \
+        if world > 1 else (None, None)
     out = torch.empty((n, hq * D), dtype=torch.bfloat16, device=dev) if world == 1 else None
 
     cfg = tmx.TriangleMixConfig(SI, SL, LAST, triangle_layer_indices=list(TRIANGLE_LAYERS))
@@ -460,8 +463,12 @@ def main():
                     "ms_per_step_with": ms_per_step, "ms_per_step_without": no_gather_ms,
                     "exposed_ms_per_step": ms_per_step - no_gather_ms,
                     "bytes_per_rank_per_layer": n * hq * D * 2,
-                    "how": "NCCL all_gather_into_tensor of each layer's [T, Hq/P, D] output shard, asynchronous, "
-                           "double-buffered (head_shard.OverlappedGather)"},
+                    "kind": gather_kind,
+                    "how": ("every rank pushes each layer's [T, Hq/P, D] output shard into the peers' symmetric-memory "
+                            "gather buffers with copy-engine peer copies on a side stream + device barrier "
+                            "(head_shard.PeerGather)") if gather_kind == "peer" else
+                           ("NCCL all_gather_into_tensor of each layer's [T, Hq/P, D] output shard, asynchronous, "
+                            "double-buffered (head_shard.OverlappedGather)")},
                 "prologue": prologue,
                 "roofline": {"bound": "tensor", "kernel": "dense-causal attention layer (per rank)",
                              "achieved": achieved, "peak": peaks["tflops"], "unit": "TFLOP/s",

@@ -62,6 +62,24 @@ def main():
             torch.cuda.synchronize()
             gather_ms = e0.elapsed_time(e1)
             full = head_shard.heads_from_gathered(gathered)
+            # the same gather by NVLink peer-memory pushes (head_shard.PeerGather): identical bytes, timed
+            peer_ms, peer_same = None, None
+            try:
+                pg = head_shard.PeerGather((t, part.num_heads * d), torch.bfloat16, dev, depth=1)
+                for rep in range(3):
+                    pg.buffer(rep).copy_(out)
+                    torch.cuda.synchronize()
+                    dist.barrier()
+                    e0.record()
+                    pg.launch(rep)
+                    pg.finish()
+                    e1.record()
+                    torch.cuda.synchronize()
+                peer_ms = e0.elapsed_time(e1)
+                peer_same = bool(torch.equal(pg.result(0).view(-1), gathered.view(-1)))
+                del pg
+            except Exception as e:      # noqa: BLE001
+                peer_same = "unavailable: %s" % (e,)
             if rank == 0:
                 one = tmx.TriangleMixImpl(hq_tot, d, d ** -0.5, num_kv_heads=hkv_tot, trianglemix_config=cfg,
                                           layer_idx=layer_idx, num_layers=2)
@@ -84,7 +102,10 @@ def main():
                 ok = same if layer_idx == 0 else (viol == 0 and stray == 0)
                 results.append({"case": name, "layer": "triangle" if layer_idx == 1 else "dense", "world": world,
                                 "tokens": t, "heads_per_rank": [part.num_heads, part.num_kv_heads],
-                                "ok": bool(ok), "bit_identical_to_1gpu": bool(same),
+                                "ok": bool(ok) and peer_same is not False, "bit_identical_to_1gpu": bool(same),
+                                "peer_gather_identical_to_nccl": peer_same, "peer_gather_ms": peer_ms,
+                                "peer_gather_GBps_per_rank": None if not peer_ms else
+                                (world - 1) * t * part.num_heads * d * 2 / peer_ms / 1e6,
                                 "max_abs_diff": float(diff.max().item()), "tolerance_violations": viol,
                                 "rows_differing": int(rows_diff.sum().item()),
                                 "rows_differing_outside_dense_tail": stray, "all_gather_ms": gather_ms,
