@@ -263,3 +263,31 @@ def error_report(out, ref, atol: float = 1.5e-2, rtol: float = 1e-2) -> dict:
             "fro_rel": float(torch.linalg.vector_norm(o - r) /
                              max(float(torch.linalg.vector_norm(r)), 1e-30)),
             "violations": viol, "numel": o.numel()}
+
+
+# --------------------------------------------------------------------------
+# Middle Q-K gradient (what the reference's TriangleMixAnalyzer consumes, trianglemix_attention.py:358-373;
+# the reference has no producer -- this is the definition the GPU producer is checked against)
+# --------------------------------------------------------------------------
+def middle_gate_gradient_autograd(q, k, v, d_out, scale: float, si: int, sl: int, last: int):
+    """dL/dg per (row, head) by autograd, for ONE sequence: the reference op's arithmetic
+    (ascend_trianglemix.py:86-106, fp32) with the additive mask  0 on the triangle piece, log(g) on the
+    middle piece (_create_middle_mask, :133-171), -inf elsewhere, L = sum(out * d_out), at g = 1.
+    One gate per (row, head) so that the per-row gradients come out of a single backward.
+    q, d_out [N, Hq, D]; k, v [N, Hkv, D].  Returns float32 [N, Hq]."""
+    import torch
+    n, hq, _ = q.shape
+    hkv = k.shape[1]
+    tri = torch.from_numpy(piece_closed("triangle", n, si, sl, last).astype(np.float32))
+    mid = torch.from_numpy(piece_closed("middle", n, si, sl, last).astype(np.float32))
+    g = torch.ones(hq, n, 1, dtype=torch.float32, requires_grad=True)
+    qf = q.float().transpose(0, 1)
+    kf = k.float().repeat_interleave(hq // hkv, dim=1).transpose(0, 1)
+    vf = v.float().repeat_interleave(hq // hkv, dim=1).transpose(0, 1)
+    scores = torch.matmul(qf, kf.transpose(-2, -1)) * scale
+    add = torch.where(tri > 0, torch.zeros(()), torch.full((), -float("inf"))) .unsqueeze(0) .expand(hq, n, n)
+    add = torch.where(mid.unsqueeze(0) > 0, torch.log(g).expand(hq, n, n), add)
+    w = torch.softmax(scores + add, dim=-1)
+    out = torch.matmul(w, vf).transpose(0, 1)
+    (out * d_out.float()).sum().backward()
+    return g.grad[:, :, 0].transpose(0, 1).contiguous()

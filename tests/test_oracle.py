@@ -128,3 +128,26 @@ def test_error_report():
     b[0, 0] = 1.0
     rep = orc.error_report(a, b)
     assert rep["violations"] == 1 and rep["max_abs"] == 1.0 and abs(rep["fro_rel"] - 1.0) < 1e-6
+
+
+def test_middle_gate_gradient_closed_form_equals_autograd():
+    """The identity the GPU producer uses (vllm_trianglemix_b200/layer_selection.py): dL/dg = dO . m (1 - m)
+    (O_mid - O_tri) with m = sigmoid(lse_mid - lse_tri), against autograd over the reference op's arithmetic."""
+    import torch
+    torch.manual_seed(0)
+    n, hq, hkv, si, sl, last = 200, 4, 2, 3, 9, 17
+    q, k, v, do = (torch.randn(n, h, 128).bfloat16() for h in (hq, hkv, hkv, hq))
+    scale = 128 ** -0.5
+    g = orc.middle_gate_gradient_autograd(q, k, v, do, scale, si, sl, last)
+    tri = torch.from_numpy(orc.additive(orc.piece_closed("triangle", n, si, sl, last).astype(np.float32)))
+    mid = torch.from_numpy(orc.additive(orc.piece_closed("middle", n, si, sl, last).astype(np.float32)))
+    qf = q.float().transpose(0, 1)
+    kf = k.float().repeat_interleave(hq // hkv, 1).transpose(0, 1)
+    vf = v.float().repeat_interleave(hq // hkv, 1).transpose(0, 1)
+    s = torch.matmul(qf, kf.transpose(-2, -1)) * scale
+    m = torch.nan_to_num(torch.sigmoid(torch.logsumexp(s + mid, -1) - torch.logsumexp(s + tri, -1)))
+    o_t = torch.matmul(torch.softmax(s + tri, -1), vf)
+    o_m = torch.nan_to_num(torch.matmul(torch.softmax(s + mid, -1), vf))
+    g2 = (m * (1 - m) * ((o_m - o_t) * do.float().transpose(0, 1)).sum(-1)).transpose(0, 1)
+    assert float((g - g2).abs().max()) < 1e-4
+    assert float(g.abs().max()) > 1e-2

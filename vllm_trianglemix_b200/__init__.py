@@ -15,11 +15,12 @@ from .trianglemix_config import TriangleMixInferenceConfig
 from .backend import (TriangleMixBackend, TriangleMixImpl, TriangleMixMetadata,
                       TriangleMixMetadataBuilder)
 from .qwen3_attention import Qwen3TriangleMixAttention, compute_cos_sin_cache
+from .layer_selection import TriangleLayerSelector, middle_qk_gradient
 from ._lib import TmxError
 
 __all__ = [
     "TriangleMixConfig", "TriangleMixMaskGenerator", "TriangleMixAttention", "TriangleMixAnalyzer",
     "AscendTriangleMixAttention", "AscendNPUTriangleMixOptimizer", "create_trianglemix_config_from_hf",
     "TriangleMixInferenceConfig", "TriangleMixBackend", "TriangleMixImpl", "TriangleMixMetadata",
-    "TriangleMixMetadataBuilder", "Qwen3TriangleMixAttention", "compute_cos_sin_cache", "TmxError",
+    "TriangleMixMetadataBuilder", "Qwen3TriangleMixAttention", "compute_cos_sin_cache", "TmxError", "TriangleLayerSelector", "middle_qk_gradient",
 ]
