@@ -218,6 +218,25 @@ int tmx_reshape_and_cache_flash(const void* key, const void* value, void* k_cach
                                 int64_t cache_block_stride, int64_t cache_token_stride,
                                 int64_t cache_head_stride, int block_size, tmx_stream_t stream);
 
+/* ---- the step after attention --------------------------------------------
+ * o_proj as a row-parallel GEMM whose epilogue is the reduce-scatter: C = A W^T (bf16 in, fp32 accumulation in
+ * TMEM, bf16 out) replaces RowParallelLinear.forward's matmul (vllm/model_executor/layers/linear.py:1197-1359;
+ * call site `self.o_proj(attn_output)`, vllm/model_executor/models/qwen3.py:190), and instead of the
+ * all-reduce at linear.py:1359 every output tile is written by TMA store into the staging buffer of the rank
+ * that owns its token rows -- device pointers that may be PEER memory (NVLink / NVSwitch) -- then
+ * tmx_sum_partials adds the n_slots partials of the owned rows.
+ *   a [M, K] (row stride a_stride), w [N, K] (row stride w_stride): K contiguous; N % 256 == 0, K % 64 == 0.
+ *   n_dest == 1: out_ptrs_host[0] is C [M, N] (row stride out_stride).
+ *   n_dest  > 1: rows [d * rows_per_dest, (d+1) * rows_per_dest) of C go to out_ptrs_host[d], a contiguous
+ *                [n_slots, rows_per_dest, N] bf16 buffer, at slot `slot` (rows_per_dest % 128 == 0).
+ * out_ptrs_host is a HOST array of n_dest (<= 8) device pointers. */
+int tmx_linear_bf16(void* const* out_ptrs_host, int n_dest, int slot, int n_slots, int64_t rows_per_dest,
+                    const void* a, const void* w, int M, int N, int K, int64_t a_stride, int64_t w_stride,
+                    int64_t out_stride, tmx_stream_t stream);
+/* out[r, :] = sum_s partials[s, r, :]  (partials [n_slots, rows, N] bf16 contiguous, fp32 accumulation). */
+int tmx_sum_partials(void* out, const void* partials, int n_slots, int64_t rows, int N, int64_t out_stride,
+                     tmx_stream_t stream);
+
 /* Number of kernels the last tmx_prefill_attn call on this thread enqueued
  * (bench.py's gpu_launches accounting). */
 int tmx_last_launch_count(void);

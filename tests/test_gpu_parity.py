@@ -345,3 +345,39 @@ def test_registered_torch_op_matches_ctypes_path(ops):
 
     c = torch.compile(f, fullgraph=True, backend="eager")(qd, kd, vd)
     assert torch.equal(c, ops.prefill_attn(qd, kd, vd, cu, n, 0.088, 4, 32, 64, ops.TRIANGLE))
+
+
+# ------------------------------------------------------------------ o_proj GEMM (the step after attention)
+@pytest.mark.parametrize("m,n,k", [(128, 256, 64), (1000, 512, 256), (4096, 4096, 512), (333, 1024, 4096), (1, 256, 128),
+                                   (8192, 5120, 1024)])
+def test_linear_vs_fp32_matmul(ops, m, n, k):
+    """C = A W^T on tcgen05 against the fp32 matmul of the same bf16 inputs (what RowParallelLinear computes,
+    linear.py:1197-1359).  bf16 output of an fp32 accumulation: |err| <= 2^-8 |ref| + accumulation noise."""
+    g = torch.Generator().manual_seed(m + n + k)
+    a = torch.randn(m, k, generator=g).bfloat16()
+    w = (torch.randn(n, k, generator=g) * k ** -0.5).bfloat16()
+    out = ops.linear(a.to(DEV), w.to(DEV)).cpu().float()
+    ref = a.float() @ w.float().t()
+    assert out.shape == (m, n)
+    assert torch.allclose(out, ref, atol=1e-2, rtol=1e-2), float((out - ref).abs().max())
+    assert float((out - ref).norm() / ref.norm()) < 4e-3
+    # strided input: a slice of a wider buffer, as attn_output is a view of the attention layer's output
+    wide = torch.randn(m, k + 64, generator=g).bfloat16().to(DEV)
+    out2 = ops.linear(wide[:, :k], w.to(DEV)).cpu().float()
+    assert torch.allclose(out2, wide[:, :k].cpu().float() @ w.float().t(), atol=1e-2, rtol=1e-2)
+
+
+def test_linear_scatter_and_sum_single_process(ops):
+    """The fused reduce-scatter epilogue with local buffers standing in for the peers: 4 'ranks' x 256 rows."""
+    world, rows, n, k = 4, 256, 512, 128
+    g = torch.Generator().manual_seed(5)
+    ws = [(torch.randn(n, k, generator=g) * k ** -0.5).bfloat16().to(DEV) for _ in range(world)]
+    xs = [torch.randn(world * rows, k, generator=g).bfloat16().to(DEV) for _ in range(world)]
+    staging = [torch.zeros(world, rows, n, dtype=torch.bfloat16, device=DEV) for _ in range(world)]
+    for r in range(world):          # "rank" r pushes its partial of every row block into the owner's slot r
+        ops.linear_scatter(xs[r], ws[r], [s.data_ptr() for s in staging], r, world, rows)
+    total = sum(x.float() @ w.float().t() for x, w in zip(xs, ws))
+    for o in range(world):
+        got = ops.sum_partials(staging[o]).cpu().float()
+        ref = total[o * rows:(o + 1) * rows].cpu()
+        assert torch.allclose(got, ref, atol=3e-2, rtol=2e-2), float((got - ref).abs().max())

@@ -37,6 +37,8 @@ SIGNATURES = {
                                 _i64, _i64, _i64, _i32, _vp]),
     "tmx_reshape_and_cache_flash": (_i32, [_vp, _vp, _vp, _vp, _vp, _i32, _i32, _i32, _i64, _i64,
                                            _i64, _i64, _i64, _i32, _vp]),
+    "tmx_linear_bf16": (_i32, [_vp, _i32, _i32, _i32, _i64, _vp, _vp, _i32, _i32, _i32, _i64, _i64, _i64, _vp]),
+    "tmx_sum_partials": (_i32, [_vp, _vp, _i32, _i64, _i32, _i64, _vp]),
     "tmx_last_launch_count": (_i32, []),
 }
 

@@ -210,3 +210,48 @@ def make_gather(kind: str, shard_shape, dtype, device, depth: int = 2, group=Non
             import sys
             print("PeerGather unavailable (%s: %s); using ncclAllGather" % (type(e).__name__, e), file=sys.stderr)
     return OverlappedGather(shard_shape, dtype, device, depth, group), "nccl"
+
+
+class RowParallelOProj:
+    """o_proj under head sharding with the reduce-scatter fused into the GEMM.
+
+    Reference: `output, _ = self.o_proj(attn_output)` (vllm/model_executor/models/qwen3.py:190) is a
+    RowParallelLinear (vllm/model_executor/layers/linear.py:1197-1359): every rank multiplies its
+    [T, Hq/P * D] attention shard with its [hidden, Hq/P * D] weight shard and the partial results are
+    all-reduced (:1359).  Here rank r owns the token rows [r * T/P, (r + 1) * T/P): the GEMM's epilogue
+    TMA-stores every partial tile straight into the owner's staging buffer [P, T/P, hidden] (slot = source
+    rank) over NVLink peer memory -- the transfer rides behind the math tile by tile -- a device barrier
+    follows, and the owner adds its P partials in fp32 (ops.sum_partials).  `forward` returns the rank's
+    [T/P, hidden] rows (reduce-scatter); `all_gather=True` pushes them to every rank (the all-reduce value).
+    Needs T % (128 * P) == 0 (token rows are padded by the caller otherwise)."""
+
+    def __init__(self, weight_shard: torch.Tensor, tokens: int, device, group=None):
+        import torch.distributed._symmetric_memory as symm_mem
+        self.group = group if group is not None else dist.group.WORLD
+        self.world = dist.get_world_size(self.group)
+        self.rank = dist.get_rank(self.group)
+        self.weight = weight_shard
+        self.hidden = weight_shard.shape[0]
+        if tokens % (128 * self.world) != 0:
+            raise ValueError("tokens (%d) must be a multiple of 128 * world (%d)" % (tokens, 128 * self.world))
+        self.tokens, self.rows = tokens, tokens // self.world
+        self.staging = symm_mem.empty((self.world, self.rows, self.hidden), dtype=torch.bfloat16, device=device)
+        self.handle = symm_mem.rendezvous(self.staging, self.group.group_name)
+        self.dest_ptrs = [self.handle.get_buffer(p, self.staging.shape, torch.bfloat16).data_ptr()
+                          for p in range(self.world)]
+        self.full = None
+
+    def forward(self, attn_shard: torch.Tensor, all_gather: bool = False) -> torch.Tensor:
+        from . import ops
+        assert attn_shard.shape[0] == self.tokens
+        self.handle.barrier(channel=0)                 # every rank is done reading its staging buffer
+        ops.linear_scatter(attn_shard, self.weight, self.dest_ptrs, self.rank, self.world, self.rows)
+        self.handle.barrier(channel=1)                 # every rank's partial tiles have landed everywhere
+        mine = ops.sum_partials(self.staging)
+        if not all_gather:
+            return mine
+        if self.full is None:
+            self.full = PeerGather((self.rows, self.hidden), torch.bfloat16, mine.device, depth=1, group=self.group)
+        self.full.buffer(0).copy_(mine)
+        self.full.launch(0)
+        return self.full.result(0).view(self.tokens, self.hidden)

@@ -365,5 +365,60 @@ def qk_norm_rope(positions: torch.Tensor, q: torch.Tensor, k: torch.Tensor, q_we
     return q_out, k_out
 
 
+def linear(x: torch.Tensor, weight: torch.Tensor, out: Optional[torch.Tensor] = None) -> torch.Tensor:
+    """y = x @ weight.T in bf16 (fp32 accumulation on tcgen05): the matmul of the reference's o_proj,
+    RowParallelLinear.forward (vllm/model_executor/layers/linear.py:1197-1359), for this rank's shard.
+    x [M, K], weight [N, K] (torch.nn.Linear layout), both bf16 with contiguous rows; N % 256 == 0, K % 64 == 0."""
+    device = _require_cuda(x.device)
+    lib = _lib.load()
+    if x.dtype != torch.bfloat16 or weight.dtype != torch.bfloat16 or x.dim() != 2 or weight.dim() != 2 \
+            or x.shape[1] != weight.shape[1]:
+        raise _lib.TmxError("linear needs bf16 x [M, K] and weight [N, K]; got %r %r" % (tuple(x.shape), tuple(weight.shape)))
+    if x.stride(1) != 1:
+        x = x.contiguous()
+    if weight.stride(1) != 1:
+        weight = weight.contiguous()
+    m, k = x.shape
+    n = weight.shape[0]
+    if out is None:
+        out = torch.empty((m, n), dtype=torch.bfloat16, device=device)
+    import ctypes
+    ptrs = (ctypes.c_void_p * 1)(out.data_ptr())
+    with torch.cuda.device(device):
+        st = lib.tmx_linear_bf16(ptrs, 1, 0, 1, m, x.data_ptr(), weight.data_ptr(), m, n, k, x.stride(0),
+                                 weight.stride(0), out.stride(0), _stream(device))
+    _lib.check(st, "tmx_linear_bf16")
+    return out
+
+
+def linear_scatter(x: torch.Tensor, weight: torch.Tensor, dest_ptrs, slot: int, n_slots: int, rows_per_dest: int) -> None:
+    """The same GEMM with the reduce-scatter fused into its epilogue: rows [d * rows_per_dest, ...) of the
+    result are TMA-stored into dest_ptrs[d] (device pointers, possibly peer memory), a [n_slots, rows_per_dest, N]
+    bf16 staging buffer, at slot `slot`.  See head_shard.RowParallelOProj."""
+    device = _require_cuda(x.device)
+    lib = _lib.load()
+    import ctypes
+    m, k = x.shape
+    n = weight.shape[0]
+    ptrs = (ctypes.c_void_p * len(dest_ptrs))(*[int(p) for p in dest_ptrs])
+    with torch.cuda.device(device):
+        st = lib.tmx_linear_bf16(ptrs, len(dest_ptrs), slot, n_slots, rows_per_dest, x.data_ptr(), weight.data_ptr(),
+                                 m, n, k, x.stride(0), weight.stride(0), n, _stream(device))
+    _lib.check(st, "tmx_linear_bf16")
+
+
+def sum_partials(partials: torch.Tensor, out: Optional[torch.Tensor] = None) -> torch.Tensor:
+    """[S, R, N] bf16 -> [R, N] bf16, fp32 accumulation (the reduction half of the fused reduce-scatter)."""
+    device = _require_cuda(partials.device)
+    lib = _lib.load()
+    s, r, n = partials.shape
+    if out is None:
+        out = torch.empty((r, n), dtype=torch.bfloat16, device=device)
+    with torch.cuda.device(device):
+        st = lib.tmx_sum_partials(out.data_ptr(), partials.data_ptr(), s, r, n, out.stride(0), _stream(device))
+    _lib.check(st, "tmx_sum_partials")
+    return out
+
+
 def last_launch_count() -> int:
     return _lib.load().tmx_last_launch_count()
