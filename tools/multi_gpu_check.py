@@ -113,6 +113,53 @@ def main():
                 print(json.dumps(results[-1]), flush=True)
                 del ref
             del gathered, full, out
+    # ---- o_proj with the reduce-scatter fused into the GEMM epilogue (head_shard.RowParallelOProj) against
+    # torch.matmul + NCCL: the reference's RowParallelLinear value (linear.py:1197-1359) ----------------------
+    try:
+        t, hidden, hq_tot = min(args.n, 65536), 4096, 32
+        kshard = hq_tot * d // world
+        g = torch.Generator().manual_seed(77)
+        x_full = torch.randn(t, hq_tot * d, generator=g).bfloat16()
+        w_full = (torch.randn(hidden, hq_tot * d, generator=g) * (hq_tot * d) ** -0.5).bfloat16()
+        xs = x_full[:, rank * kshard:(rank + 1) * kshard].contiguous().to(dev)
+        ws = w_full[:, rank * kshard:(rank + 1) * kshard].contiguous().to(dev)
+        oproj = head_shard.RowParallelOProj(ws, t, dev)
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        for rep in range(3):
+            torch.cuda.synchronize(); dist.barrier()
+            e0.record()
+            mine = oproj.forward(xs)
+            e1.record()
+            torch.cuda.synchronize()
+        fused_ms = e0.elapsed_time(e1)
+        full = oproj.forward(xs, all_gather=True).clone()
+        # NCCL formulation: local matmul, reduce-scatter (and all-reduce for the full value)
+        for rep in range(3):
+            torch.cuda.synchronize(); dist.barrier()
+            e0.record()
+            part = torch.matmul(xs, ws.t())
+            rs = torch.empty(t // world, hidden, dtype=torch.bfloat16, device=dev)
+            dist.reduce_scatter_tensor(rs, part)
+            e1.record()
+            torch.cuda.synchronize()
+        nccl_ms = e0.elapsed_time(e1)
+        ref = (x_full.float() @ w_full.float().t())
+        ref_mine = ref[rank * (t // world):(rank + 1) * (t // world)].to(dev)
+        err = (mine.float() - ref_mine).abs()
+        okp = bool((err <= 3e-2 + 2e-2 * ref_mine.abs()).all()) and bool(
+            ((full.float() - ref.to(dev)).abs() <= 3e-2 + 2e-2 * ref.to(dev).abs()).all())
+        flag = torch.tensor([1 if okp else 0], device=dev)
+        dist.all_reduce(flag, op=dist.ReduceOp.MIN)
+        if rank == 0:
+            results.append({"case": "o_proj_fused_reduce_scatter", "world": world, "tokens": t, "hidden": hidden,
+                            "k_per_rank": kshard, "ok": bool(flag.item()), "max_abs_err_vs_fp32": float(err.max().item()),
+                            "fused_gemm_reduce_scatter_ms": fused_ms, "matmul_plus_nccl_reduce_scatter_ms": nccl_ms,
+                            "nccl_result_max_abs_diff": float((rs.float() - mine.float()).abs().max().item())})
+            print(json.dumps(results[-1]), flush=True)
+    except Exception as e:      # noqa: BLE001
+        if rank == 0:
+            results.append({"case": "o_proj_fused_reduce_scatter", "ok": False, "error": "%s: %s" % (type(e).__name__, e)})
+            print(json.dumps(results[-1]), flush=True)
     if rank == 0:
         ok = all(r["ok"] for r in results)
         if args.out:
