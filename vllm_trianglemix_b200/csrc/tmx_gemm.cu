@@ -48,6 +48,10 @@ struct GemmParams {
   int n_dest;                     // destination buffers (1: everything goes to out[0])
   int rows_per_dest;              // token rows owned by one destination (multiple of 128 when n_dest > 1)
   int slot;                       // this rank's slot in a destination's staging buffer [n_slots][rows_per_dest][N]
+  int m_rot;                      // row-block rotation of the tile walk: rank r starts with the rows of rank r + 1, so
+                                  // that at any moment the P ranks store into P different peers (all ranks walking
+                                  // rank 0's rows first funnels every store through ONE GPU's NVLink ingress:
+                                  // measured 2.08 ms vs 1.02 ms for matmul + ncclReduceScatter at P = 8)
 };
 
 __device__ __forceinline__ uint32_t pack2g(float lo, float hi) {
@@ -90,7 +94,7 @@ gemm_bf16_kernel(const GemmParams p, const __grid_constant__ GemmMaps maps) {
     if (ptx::elect_one()) {
       int it = 0;
       for (int tile = blockIdx.x; tile < n_tiles_total; tile += gridDim.x) {
-        const int m0 = (tile / p.n_tiles) * kBM, n0 = (tile % p.n_tiles) * kBN;
+        const int m0 = ((tile / p.n_tiles + p.m_rot) % p.m_tiles) * kBM, n0 = (tile % p.n_tiles) * kBN;
         for (int ks = 0; ks < k_steps; ++ks, ++it) {
           const int st = it % kStagesG;
           if (it >= kStagesG) ptx::mbar_wait(bar(gEmpty + st), ((it / kStagesG) - 1) & 1);
@@ -137,7 +141,7 @@ gemm_bf16_kernel(const GemmParams p, const __grid_constant__ GemmMaps maps) {
     int local = 0, slab_count = 0;
     for (int tile = blockIdx.x; tile < n_tiles_total; tile += gridDim.x, ++local) {
       const int b = local & 1;
-      const int m0 = (tile / p.n_tiles) * kBM, n0 = (tile % p.n_tiles) * kBN;
+      const int m0 = ((tile / p.n_tiles + p.m_rot) % p.m_tiles) * kBM, n0 = (tile % p.n_tiles) * kBN;
       // destination: the rank that owns these token rows; our partial goes to slot `slot` of its buffer
       const int dest = p.n_dest > 1 ? m0 / p.rows_per_dest : 0;
       const int drow = p.n_dest > 1 ? p.slot * p.rows_per_dest + (m0 - dest * p.rows_per_dest) : m0;
@@ -247,6 +251,7 @@ extern "C" int tmx_linear_bf16(void* const* out_ptrs_host, int n_dest, int slot,
   p.M = M; p.N = N; p.K = K;
   p.m_tiles = (M + kBM - 1) / kBM; p.n_tiles = N / kBN;
   p.n_dest = n_dest; p.rows_per_dest = (int)(n_dest > 1 ? rows_per_dest : M); p.slot = slot;
+  p.m_rot = n_dest > 1 ? (int)((((int64_t)(slot + 1) % n_dest) * (rows_per_dest / kBM)) % p.m_tiles) : 0;
   TMX_SET_SMEM_ATTR(gemm_bf16_kernel, kAttrGemm, kSmemG);
   const int tiles = p.m_tiles * p.n_tiles, sms = device_sm_count();
   gemm_bf16_kernel<<<tiles < sms ? tiles : sms, kThreadsG, kSmemG, (cudaStream_t)stream>>>(p, maps);
