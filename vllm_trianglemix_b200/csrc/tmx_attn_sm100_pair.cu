@@ -641,12 +641,12 @@ int launch_attn_sm100_pair(const AttnParams& p, cudaStream_t s) {
   int slot = kAttrV3Pair;
   bool ahead = true;
 #ifdef TMX_DEV
-  // TMX_SM100_VARIANT (developer build): bits 0-1 = exponentials on the FMA pipe per 16 (0, 4, 6, 8),
+  // TMX_SM100_VARIANT (developer build): bits 0-1 = exponentials on the FMA pipe per 16 (0, 4, 6, 2 look-ahead / 8 classic),
   // bit 2 = classic schedule (one N = 128 score MMA per tile) instead of look-ahead
   {
     const int v = sm100_variant();
     static const Kern ahead_k[4] = {attn_sm100_pair_kernel<0, true>, attn_sm100_pair_kernel<4, true>,
-                                    attn_sm100_pair_kernel<6, true>, attn_sm100_pair_kernel<8, true>};
+                                    attn_sm100_pair_kernel<6, true>, attn_sm100_pair_kernel<2, true>};
     static const Kern classic_k[4] = {attn_sm100_pair_kernel<0, false>, attn_sm100_pair_kernel<4, false>,
                                       attn_sm100_pair_kernel<6, false>, attn_sm100_pair_kernel<8, false>};
     if (v != 0) { ahead = (v & 4) == 0; kern = ahead ? ahead_k[v & 3] : classic_k[v & 3]; slot = -1; }

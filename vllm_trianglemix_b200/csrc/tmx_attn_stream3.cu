@@ -38,16 +38,18 @@ constexpr int kSinkKeys = 16;
 constexpr int kMaxWin = 112;
 constexpr int kThreads3 = 384;
 constexpr int kQBytes = 2 * 128 * 128;           // [128 packed rows][128 d] bf16, two 64-d panels
-constexpr int kStagesMax = 3;
-constexpr int kSmemBudget = 225 * 1024;
+constexpr int kMaxQ = 3, kMaxKV = 4;              // ring depths (Q slots / K-V-O slots)
+constexpr int kSmemBudget = 226 * 1024;
 constexpr uint32_t kColSink = 0, kColWin = 16, kColOut = 128, kColsPerSet = 256;
 // bf16 P: its own columns [80, 120) while the scores fit below them (nW <= 64), so that the next
 // scores of a set may be issued as soon as the softmax has READ the old ones; wider windows overlay
 // P on the score columns and the next scores wait for PV.
 constexpr uint32_t kColPSep = 80;
 
-// barriers: full[3] empty[3] staged[3] sfull[2] pready[2] ofull[2]
-constexpr int bFull = 0, bEmpty = 3, bStaged = 6, bSFull = 9, bPReady = 11, bOFull = 13, kNumBars3 = 15;
+// barriers: qfull[3] qempty[3] kvfull[4] kvempty[4] staged[4] sfull[2] pready[2] ofull[2]
+constexpr int bQFull = 0, bQEmpty = bQFull + kMaxQ, bKVFull = bQEmpty + kMaxQ, bKVEmpty = bKVFull + kMaxKV,
+              bStaged = bKVEmpty + kMaxKV, bSFull = bStaged + kMaxKV, bPReady = bSFull + 2, bOFull = bPReady + 2,
+              kNumBars3 = bOFull + 2;
 
 struct Stream3Maps {
   CUtensorMap q, kw, vw, ks, vs, o;
@@ -88,27 +90,30 @@ __device__ __forceinline__ Tile tile_at(const AttnParams& p, unsigned L, int TT)
   return t;
 }
 
-// kDirect: the epilogue writes O straight from registers to global memory (32-byte stores) and the
-// stage returns to the producer when PV completes (tcgen05.commit); otherwise O is staged in the stage's
-// dead Q buffer and leaves by TMA store, and the stage is held until the store has read it.
-template <int NWC, bool kDirect>
+// Two rings of shared-memory slots: Q (32 KB, free again as soon as the score MMA has read it) and K|V (free
+// when the tile's O, staged over the dead K/V bytes, has left by TMA store).  A tile's Q slot lives ~4800 clk, its
+// K/V/O slot ~9700 (profiles/r02_stream3_experiments.md), so 2 + 4 slots keep four tiles in flight per SM in the
+// 224 KB that three whole-tile stages used to take.
+template <int NWC>
 __global__ void __launch_bounds__(kThreads3, 1)
 attn_stream3_kernel(const AttnParams p, const __grid_constant__ Stream3Maps maps, const int G,
-                    const int n_stages, const unsigned n_items) {
+                    const int n_q, const int n_kv, const unsigned n_items) {
   constexpr int nW = NWC * 16;
   // K (and V) of a tile: two 64-d panels of [16 sink keys | nW window keys] rows of 128 bytes, so that the
   // scores of sink + window are ONE N = 16 + nW MMA per k-step and PV walks 1 + NWC uniform 16-key steps
   constexpr int kvPanel = (kSinkKeys + nW) * 128;
   constexpr int kvBytes = 2 * kvPanel;                         // K or V of one tile
-  constexpr uint32_t stageBytes = (uint32_t)(kQBytes + 2 * kvBytes);
+  constexpr uint32_t kvSlot = (uint32_t)(2 * kvBytes > kQBytes ? 2 * kvBytes : kQBytes);   // K | V, or the staged O tile
   constexpr bool kSepP = NWC <= 4;
   constexpr uint32_t kColP = kSepP ? kColPSep : 0u;
   extern __shared__ uint8_t smem_raw[];
   const uint32_t smem_base = (ptx::smem_u32(smem_raw) + 1023u) & ~1023u;
-  const uint32_t sBar = smem_base + (uint32_t)n_stages * stageBytes;
+  const uint32_t sKV = smem_base + (uint32_t)n_q * kQBytes;
+  const uint32_t sBar = sKV + (uint32_t)n_kv * kvSlot;
   const uint32_t sTmemPtr = sBar + kNumBars3 * 8;
   auto bar = [&](int i) { return sBar + 8u * (uint32_t)i; };
-  auto stage_base = [&](int st) { return smem_base + (uint32_t)st * stageBytes; };
+  auto q_slot = [&](int t) { return smem_base + (uint32_t)(t % n_q) * kQBytes; };
+  auto kv_slot = [&](int t) { return sKV + (uint32_t)(t % n_kv) * kvSlot; };
   const int warp = __shfl_sync(0xffffffffu, (int)(threadIdx.x >> 5), 0);
   const int lane = threadIdx.x & 31;
   const int TT = 128 / G;
@@ -116,8 +121,9 @@ attn_stream3_kernel(const AttnParams p, const __grid_constant__ Stream3Maps maps
   if (warp == 8 && lane == 0) {
     ptx::prefetch_tmap(&maps.q); ptx::prefetch_tmap(&maps.kw); ptx::prefetch_tmap(&maps.vw);
     ptx::prefetch_tmap(&maps.ks); ptx::prefetch_tmap(&maps.vs); ptx::prefetch_tmap(&maps.o);
-    for (int s = 0; s < kStagesMax; ++s) {
-      ptx::mbar_init(bar(bFull + s), 1); ptx::mbar_init(bar(bEmpty + s), 1); ptx::mbar_init(bar(bStaged + s), 4);
+    for (int s = 0; s < kMaxQ; ++s) { ptx::mbar_init(bar(bQFull + s), 1); ptx::mbar_init(bar(bQEmpty + s), 1); }
+    for (int s = 0; s < kMaxKV; ++s) {
+      ptx::mbar_init(bar(bKVFull + s), 1); ptx::mbar_init(bar(bKVEmpty + s), 1); ptx::mbar_init(bar(bStaged + s), 4);
     }
     for (int s = 0; s < 2; ++s) {
       ptx::mbar_init(bar(bSFull + s), 1); ptx::mbar_init(bar(bPReady + s), 4); ptx::mbar_init(bar(bOFull + s), 1);
@@ -138,19 +144,21 @@ attn_stream3_kernel(const AttnParams p, const __grid_constant__ Stream3Maps maps
       for (unsigned L = blockIdx.x; L < n_items; L += gridDim.x) {
         const Tile tl = tile_at(p, L, TT);
         if (!tl.valid) continue;
-        const int st = t % n_stages;
-        if (t >= n_stages) ptx::mbar_wait(bar(bEmpty + st), ((t / n_stages) - 1) & 1);
+        const int qs = t % n_q, ks = t % n_kv;
+        if (t >= n_q) ptx::mbar_wait(bar(bQEmpty + qs), ((t / n_q) - 1) & 1);
+        if (t >= n_kv) ptx::mbar_wait(bar(bKVEmpty + ks), ((t / n_kv) - 1) & 1);
         TMX_TRACE(0, t);
-        const uint32_t sQ = stage_base(st), sK = sQ + kQBytes, sV = sK + kvBytes;
-        const uint32_t full = bar(bFull + st);
+        const uint32_t sQ = q_slot(t), sK = kv_slot(t), sV = sK + kvBytes;
+        const uint32_t qfull = bar(bQFull + qs), kvfull = bar(bKVFull + ks);
         const int w0 = tl.r0 - p.sl, tok = tl.seq_start + tl.r0;
-        ptx::mbar_expect_tx(full, stageBytes);
+        ptx::mbar_expect_tx(qfull, kQBytes);
+        ptx::mbar_expect_tx(kvfull, 2 * kvBytes);
         for (int pnl = 0; pnl < 2; ++pnl) {
-          ptx::tma_load_3d(sQ + pnl * (128 * 128), &maps.q, full, pnl * 64, tl.kvh * G, tok);
-          ptx::tma_load_2d(sK + pnl * kvPanel, &maps.ks, full, tl.kvh * kD + pnl * 64, tl.seq_start);
-          ptx::tma_load_2d(sK + pnl * kvPanel + kSinkKeys * 128, &maps.kw, full, tl.kvh * kD + pnl * 64, tl.seq_start + w0);
-          ptx::tma_load_2d(sV + pnl * kvPanel, &maps.vs, full, tl.kvh * kD + pnl * 64, tl.seq_start);
-          ptx::tma_load_2d(sV + pnl * kvPanel + kSinkKeys * 128, &maps.vw, full, tl.kvh * kD + pnl * 64, tl.seq_start + w0);
+          ptx::tma_load_3d(sQ + pnl * (128 * 128), &maps.q, qfull, pnl * 64, tl.kvh * G, tok);
+          ptx::tma_load_2d(sK + pnl * kvPanel, &maps.ks, kvfull, tl.kvh * kD + pnl * 64, tl.seq_start);
+          ptx::tma_load_2d(sK + pnl * kvPanel + kSinkKeys * 128, &maps.kw, kvfull, tl.kvh * kD + pnl * 64, tl.seq_start + w0);
+          ptx::tma_load_2d(sV + pnl * kvPanel, &maps.vs, kvfull, tl.kvh * kD + pnl * 64, tl.seq_start);
+          ptx::tma_load_2d(sV + pnl * kvPanel + kSinkKeys * 128, &maps.vw, kvfull, tl.kvh * kD + pnl * 64, tl.seq_start + w0);
         }
         ++t;
       }
@@ -170,13 +178,14 @@ attn_stream3_kernel(const AttnParams p, const __grid_constant__ Stream3Maps maps
       // score columns are free: the softmax has read S(t-2) (kSepP: "P(t-2) stored" says so), or, when P
       // overlays the scores, PV(t-2) has consumed it.
       for (int t = 0; t < ntiles; ++t) {
-        const int st = t % n_stages, set = t & 1;
-        ptx::mbar_wait(bar(bFull + st), (t / n_stages) & 1);
+        const int set = t & 1;
+        ptx::mbar_wait(bar(bQFull + t % n_q), (t / n_q) & 1);
+        ptx::mbar_wait(bar(bKVFull + t % n_kv), (t / n_kv) & 1);
         TMX_TRACE(1, t);
         if (t >= 2) ptx::mbar_wait(bar((kSepP ? bPReady : bOFull) + set), ((t >> 1) - 1) & 1);
         ptx::tc_fence_after();
         if (ptx::elect_one()) {
-          const uint32_t sQ = stage_base(st), sK = sQ + kQBytes;
+          const uint32_t sQ = q_slot(t), sK = kv_slot(t);
           const uint64_t dQ = ptx::smem_desc(sQ, 16, 1024), dK = ptx::smem_desc(sK, 16, 1024);
           const uint32_t tc = tb + (uint32_t)set * kColsPerSet;
 #pragma unroll
@@ -184,25 +193,25 @@ attn_stream3_kernel(const AttnParams p, const __grid_constant__ Stream3Maps maps
             ptx::mma_ss(tc + kColSink, dQ + (((ks >> 2) * (128 * 128) + (ks & 3) * 32) >> 4),
                         dK + (((ks >> 2) * kvPanel + (ks & 3) * 32) >> 4), idS, ks > 0);
           ptx::mma_commit(bar(bSFull + set));
+          ptx::mma_commit(bar(bQEmpty + t % n_q));        // Q has been read: its slot may be refilled
           TMX_TRACE(2, t);
         }
         __syncwarp();
       }
     } else {
       for (int t = 0; t < ntiles; ++t) {
-        const int st = t % n_stages, set = t & 1;
+        const int set = t & 1;
         // P(t) stored => S(t) was issued (V has landed with it) and this group finished reading O(t-2)
         // (its epilogue precedes its next softmax)
         ptx::mbar_wait(bar(bPReady + set), (t >> 1) & 1);
         ptx::tc_fence_after();
         if (ptx::elect_one()) {
-          const uint64_t dV = ptx::smem_desc(stage_base(st) + kQBytes + kvBytes, kvPanel, 1024);
+          const uint64_t dV = ptx::smem_desc(kv_slot(t) + kvBytes, kvPanel, 1024);
           const uint32_t tc = tb + (uint32_t)set * kColsPerSet;
 #pragma unroll
           for (int ks = 0; ks <= NWC; ++ks)          // 16 sink keys, then the window in 16-key steps
             ptx::mma_ts(tc + kColOut, tc + kColP + (uint32_t)(ks * 8), dV + (uint64_t)((ks * 2048) >> 4), idO, ks > 0);
           ptx::mma_commit(bar(bOFull + set));
-          if constexpr (kDirect) ptx::mma_commit(bar(bEmpty + st));   // Q, K, V of the stage are dead
           TMX_TRACE(5, t);
         }
         __syncwarp();
@@ -212,22 +221,22 @@ attn_stream3_kernel(const AttnParams p, const __grid_constant__ Stream3Maps maps
     // =========================== TMA store ===========================
     // Tiles leave in order; a stage returns to the producer once its O tile has been READ out of
     // shared memory (or at once, for the edge tiles the softmax warps stored row by row).
-    if (!kDirect && ptx::elect_one()) {
+    if (ptx::elect_one()) {
       int t = 0;
       for (unsigned L = blockIdx.x; L < n_items; L += gridDim.x) {
         const Tile tl = tile_at(p, L, TT);
         if (!tl.valid) continue;
-        const int st = t % n_stages;
-        ptx::mbar_wait(bar(bStaged + st), (t / n_stages) & 1);
+        const int st = t % n_kv;
+        ptx::mbar_wait(bar(bStaged + st), (t / n_kv) & 1);
         TMX_TRACE(8, t);
         if (tl.r0 + TT <= tl.stream_end) {
-          const uint32_t sO = stage_base(st);
+          const uint32_t sO = kv_slot(t);
           ptx::tma_store_3d(&maps.o, sO, 0, tl.kvh * G, tl.seq_start + tl.r0);
           ptx::tma_store_3d(&maps.o, sO + 128 * 128, 64, tl.kvh * G, tl.seq_start + tl.r0);
           ptx::bulk_commit();
           ptx::bulk_wait_read0();
         }
-        ptx::mbar_arrive(bar(bEmpty + st));
+        ptx::mbar_arrive(bar(bKVEmpty + st));
         TMX_TRACE(9, t);
         ++t;
       }
@@ -246,7 +255,7 @@ attn_stream3_kernel(const AttnParams p, const __grid_constant__ Stream3Maps maps
       const Tile tile = tile_at(p, L, TT);
       if (!tile.valid) continue;
       if ((t & 1) != grp) { ++t; continue; }
-      const int st = t % n_stages, use = t >> 1;   // `use`: how often this TMEM set was used before
+      const int st = t % n_kv, use = t >> 1;       // `use`: how often this TMEM set was used before
       const int i = tile.r0 + m / G;
       const int head = tile.kvh * G + m % G;
       const int w0 = tile.r0 - p.sl;
@@ -320,9 +329,9 @@ attn_stream3_kernel(const AttnParams p, const __grid_constant__ Stream3Maps maps
 
       const float l = (la[0] + la[1]) + (la[2] + la[3]);
       const float inv = l > 0.f ? fast_rcp(l) : 0.f;
-      // whole tile inside the streamed rows -> TMA store through the stage's (dead) Q buffer
+      // whole tile inside the streamed rows -> TMA store, staged over the slot's (dead) K | V bytes
       const bool tma_out = tile.r0 + TT <= tile.stream_end;
-      const uint32_t sO = stage_base(st);
+      const uint32_t sO = kv_slot(t);
       __nv_bfloat16* orow = p.out + (long long)(tile.seq_start + i) * p.o_stride + head * kD;
       if (p.lse != nullptr && i < tile.stream_end)
         p.lse[(long long)head * p.total_T + tile.seq_start + i] = msc * 0.6931471805599453f + logf(l);
@@ -330,21 +339,6 @@ attn_stream3_kernel(const AttnParams p, const __grid_constant__ Stream3Maps maps
       ptx::tc_fence_after();
       if (m == 0) TMX_TRACE(6, t);
       auto emit = [&](int c, const uint32_t (&r)[32]) {
-        if constexpr (kDirect) {
-          // 32 fp32 columns -> 64 bytes of the row: two 32-byte stores (whole sectors)
-          if (i < tile.stream_end) {
-#pragma unroll
-            for (int v8 = 0; v8 < 2; ++v8) {
-              uint32_t w[8];
-#pragma unroll
-              for (int e = 0; e < 8; ++e)
-                w[e] = pack2s(__uint_as_float(r[v8 * 16 + 2 * e]) * inv, __uint_as_float(r[v8 * 16 + 2 * e + 1]) * inv);
-              asm volatile("st.global.v8.b32 [%0], {%1,%2,%3,%4,%5,%6,%7,%8};" ::"l"(orow + c * 32 + v8 * 16),
-                           "r"(w[0]), "r"(w[1]), "r"(w[2]), "r"(w[3]), "r"(w[4]), "r"(w[5]), "r"(w[6]), "r"(w[7]) : "memory");
-            }
-          }
-          return;
-        }
 #pragma unroll
         for (int v4 = 0; v4 < 4; ++v4) {
           uint4 o;
@@ -352,9 +346,7 @@ attn_stream3_kernel(const AttnParams p, const __grid_constant__ Stream3Maps maps
           o.y = pack2s(__uint_as_float(r[v4 * 8 + 2]) * inv, __uint_as_float(r[v4 * 8 + 3]) * inv);
           o.z = pack2s(__uint_as_float(r[v4 * 8 + 4]) * inv, __uint_as_float(r[v4 * 8 + 5]) * inv);
           o.w = pack2s(__uint_as_float(r[v4 * 8 + 6]) * inv, __uint_as_float(r[v4 * 8 + 7]) * inv);
-          if constexpr (kDirect) {
-            (void)o;
-          } else if (tma_out) {
+          if (tma_out) {
             // 128-byte-swizzled K-major panel layout (what the TMA box expects): 16-byte chunk ch of
             // packed row m lives at m * 128 + ((ch ^ (m & 7)) << 4) inside its 64-d panel
             const int d16 = c * 4 + v4;                     // 16-byte chunk of the 256-byte row
@@ -382,11 +374,9 @@ attn_stream3_kernel(const AttnParams p, const __grid_constant__ Stream3Maps maps
         emit(3, rb);
       }
       ptx::tc_fence_before();
-      if constexpr (!kDirect) {
-        if (tma_out) ptx::fence_proxy_async_smem();           // st.shared -> visible to the TMA store
-        __syncwarp();
-        if (lane == 0) ptx::mbar_arrive(bar(bStaged + st));    // 4 warps: tile staged (or stored row by row)
-      }
+      if (tma_out) ptx::fence_proxy_async_smem();             // st.shared -> visible to the TMA store
+      __syncwarp();
+      if (lane == 0) ptx::mbar_arrive(bar(bStaged + st));      // 4 warps: tile staged (or stored row by row)
       if (m == 0) TMX_TRACE(7, t);
       ++t;
     }
@@ -416,22 +406,16 @@ template <int NWC>
 static int launch_stream3_t(const AttnParams& p, cudaStream_t s) {
   const int G = p.Hq / p.Hkv, TT = 128 / G;
   constexpr int nW = NWC * 16;
-  constexpr int stageBytes = kQBytes + 4 * (kSinkKeys + nW) * 128;
-  int n_stages = (kSmemBudget - 2048) / stageBytes;
-  n_stages = n_stages > kStagesMax ? kStagesMax : n_stages;
-  if (n_stages < 2) return TMX_ERR_UNSUPPORTED;
-  const int smem = n_stages * stageBytes + kNumBars3 * 8 + 16 + 1024;
-  // O leaves by TMA store.  Measured round 2 (profiles/r02_stream3_experiments.md): writing it with 32-byte
-  // register stores instead releases the stage 2500 clk earlier but costs 3000 clk of epilogue per tile (one
-  // L1 wavefront per lane at the 256-byte row pitch): 587 vs 500 us.  Kept in the developer build
-  // (TMX_SM100_VARIANT bit 0) for A/B timing.
-  auto kern = attn_stream3_kernel<NWC, false>;
-  int slot = kAttrStream3 + NWC;
-#ifdef TMX_DEV
-  if (sm100_variant() & 1) { kern = attn_stream3_kernel<NWC, true>; slot = -1; }
-#endif
-  if (slot < 0) TMX_CUDA_TRY(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
-  else TMX_SET_SMEM_ATTR(kern, slot, smem);
+  constexpr int kvBytes2 = 4 * (kSinkKeys + nW) * 128;                     // K | V of one tile
+  constexpr int kvSlot = kvBytes2 > kQBytes ? kvBytes2 : kQBytes;          // ... or its staged O tile
+  // ring depths: two Q slots, as many K/V/O slots as fit (<= 4)
+  const int n_q = 2;
+  int n_kv = (kSmemBudget - 2048 - n_q * kQBytes) / kvSlot;
+  n_kv = n_kv > kMaxKV ? kMaxKV : n_kv;
+  if (n_kv < 2) return TMX_ERR_UNSUPPORTED;
+  const int smem = n_q * kQBytes + n_kv * kvSlot + kNumBars3 * 8 + 16 + 1024;
+  auto kern = attn_stream3_kernel<NWC>;
+  TMX_SET_SMEM_ATTR(kern, kAttrStream3 + NWC, smem);
   Stream3Maps maps;
   int st = tma_map_q3d(&maps.q, p.q, p.total_T, p.Hq, p.q_stride, G, TT);
   if (st == TMX_OK) st = tma_map_q3d(&maps.o, p.out, p.total_T, p.Hq, p.o_stride, G, TT);
@@ -443,7 +427,7 @@ static int launch_stream3_t(const AttnParams& p, cudaStream_t s) {
   const unsigned n_items = (unsigned)p.n_slots * (unsigned)p.Hkv;
   const unsigned sms = (unsigned)device_sm_count();
   dim3 grid(n_items < sms ? n_items : sms);
-  kern<<<grid, kThreads3, smem, s>>>(p, maps, G, n_stages, n_items);
+  kern<<<grid, kThreads3, smem, s>>>(p, maps, G, n_q, n_kv, n_items);
   count_launch();
   TMX_CUDA_TRY(cudaGetLastError());
   return TMX_OK;
