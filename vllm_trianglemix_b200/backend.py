@@ -191,6 +191,14 @@ class TriangleMixImpl:
         cache write into an earlier kernel -- Qwen3TriangleMixAttention -- enter here).
         q/k/v/out: [T, H, D] views of the actual tokens; returns `output`."""
         mode, si, sl, last = self.mask_mode()
+        cu_cpu = attn_metadata.query_start_loc_cpu
+        if cu_cpu is not None and cu_cpu.numel() > 1:
+            # the kernels size their grids from max_query_len: a value below the true maximum would leave query
+            # tiles without a worker (checked here from the CPU copy, no device sync)
+            true_max = int((cu_cpu[1:] - cu_cpu[:-1]).max())
+            if attn_metadata.max_query_len < true_max:
+                raise ValueError("attn_metadata.max_query_len (%d) is smaller than the longest query (%d)" %
+                                 (attn_metadata.max_query_len, true_max))
         if attn_metadata.context_present():
             # Chunked prefill / prefix-cache hit / decode: the keys are the cache's, through the block
             # table (flash_attn.py:518-548).  Query rows are the LAST rows of each sequence, so the
