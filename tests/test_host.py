@@ -324,3 +324,108 @@ def test_head_sharded_path_gloo_world2():
         p.join(timeout=240)
         assert p.exitcode == 0
     assert dict(ret) == {0: True, 1: True}
+
+
+# ------------------------------------------------------------------ backend host logic (no kernel runs: ops are recorded)
+class _Recorder:
+    def __init__(self):
+        self.calls = []
+
+    def prefill_attn(self, q, k, v, cu, max_seqlen, scale, si, sl, last, mode, out=None, kernel="auto", **kw):
+        self.calls.append(("prefill", q.shape[0], cu.tolist(), max_seqlen, mode))
+        return out
+
+    def chunked_prefill_attn(self, q, cu, seq_lens, max_query_len, scale, si, sl, last, mode, **kw):
+        self.calls.append(("chunked", q.shape[0], cu.tolist(), seq_lens.tolist(), max_query_len, mode,
+                           tuple(kw["block_table"].shape)))
+        return kw.get("out")
+
+
+def _impl_with_recorder(monkeypatch, layer_idx=0):
+    from vllm_trianglemix_b200 import backend
+    rec = _Recorder()
+    monkeypatch.setattr(backend.ops, "prefill_attn", rec.prefill_attn)
+    monkeypatch.setattr(backend.ops, "chunked_prefill_attn", rec.chunked_prefill_attn)
+    cfg = tmx.TriangleMixConfig(4, 32, 64, triangle_layer_indices=[0])
+    impl = tmx.TriangleMixImpl(4, 128, 0.1, num_kv_heads=2, trianglemix_config=cfg, layer_idx=layer_idx, num_layers=2)
+    return impl, rec
+
+
+def _fwd(impl, md, kv_cache=None):
+    t = md.num_actual_tokens
+    x = torch.zeros(t, 4 * 128, dtype=torch.bfloat16)
+    return impl.forward(None, x, x[:, :256], x[:, :256], kv_cache, md, output=torch.zeros_like(x))
+
+
+def test_backend_threshold_splits_mixed_batches(monkeypatch):
+    """Triangle layer: sequences <= 2048 tokens are dense-causal (reference trianglemix_attention.py:330-332), longer
+    ones triangle; runs of one class become one kernel call over a contiguous token range."""
+    impl, rec = _impl_with_recorder(monkeypatch)
+    _fwd(impl, tmx.TriangleMixMetadataBuilder.from_seq_lens([700, 100, 2600, 3000, 2048], "cpu"))
+    assert rec.calls == [("prefill", 800, [0, 700, 800], 700, ops.DENSE_CAUSAL),
+                         ("prefill", 5600, [0, 2600, 5600], 3000, ops.TRIANGLE),
+                         ("prefill", 2048, [0, 2048], 2048, ops.DENSE_CAUSAL)]
+    rec.calls.clear()
+    _fwd(impl, tmx.TriangleMixMetadataBuilder.from_seq_lens([2049, 5000], "cpu"))        # one class: one call
+    assert rec.calls == [("prefill", 7049, [0, 2049, 7049], 5000, ops.TRIANGLE)]
+    rec.calls.clear()
+    dense, rec2 = _impl_with_recorder(monkeypatch, layer_idx=1)                            # dense layer: never split
+    _fwd(dense, tmx.TriangleMixMetadataBuilder.from_seq_lens([700, 2600], "cpu"))
+    assert rec2.calls == [("prefill", 3300, [0, 700, 3300], 2600, ops.DENSE_CAUSAL)]
+
+
+def test_backend_context_path_and_checks(monkeypatch):
+    """seq_lens > query lengths (chunked prefill / prefix hit / decode) -> keys from the paged cache; without a
+    cache to read it raises instead of attending only the new tokens."""
+    impl, rec = _impl_with_recorder(monkeypatch)
+    from vllm_trianglemix_b200 import backend
+    monkeypatch.setattr(backend.ops, "reshape_and_cache_flash", lambda *a, **k: None)
+    bt = torch.zeros(3, 400, dtype=torch.int32)
+    md = tmx.TriangleMixMetadataBuilder.from_seq_lens([300, 5000, 2100], "cpu", query_lens=[1, 1000, 2100],
+                                                      block_table=bt, slot_mapping=torch.zeros(3101, dtype=torch.int64))
+    assert md.context_present()
+    with pytest.raises(NotImplementedError, match="context keys"):
+        _fwd(impl, md, kv_cache=None)
+    kv = torch.zeros(2, 4, 16, 2, 128, dtype=torch.bfloat16)
+    _fwd(impl, md, kv_cache=kv)
+    assert rec.calls == [("chunked", 1, [0, 1], [300], 1, ops.DENSE_CAUSAL, (1, 400)),
+                         ("chunked", 3100, [0, 1000, 3100], [5000, 2100], 2100, ops.TRIANGLE, (2, 400))]
+    # whole-sequence metadata is not "context"
+    assert not tmx.TriangleMixMetadataBuilder.from_seq_lens([300, 5000], "cpu").context_present()
+    # max_query_len below the longest query is refused (grids are sized from it)
+    bad = tmx.TriangleMixMetadataBuilder.from_seq_lens([300, 5000], "cpu")
+    bad.max_query_len = 4000
+    with pytest.raises(ValueError, match="max_query_len"):
+        _fwd(impl, bad)
+
+
+def test_metadata_builder_reads_common_attention_metadata():
+    """Field names of vllm/v1/attention/backends/utils.py:45-84 (duck-typed here; the reference's real class is
+    exercised in tests/test_reference_wiring.py)."""
+    import types
+    cu = torch.tensor([0, 5, 6], dtype=torch.int32)
+    common = types.SimpleNamespace(
+        query_start_loc=cu, query_start_loc_cpu=cu, seq_lens=torch.tensor([5, 40], dtype=torch.int32),
+        seq_lens_cpu=torch.tensor([5, 40], dtype=torch.int32), num_computed_tokens_cpu=torch.tensor([0, 39]),
+        num_reqs=2, num_actual_tokens=6, max_query_len=5, max_seq_len=40,
+        block_table_tensor=torch.zeros(2, 3, dtype=torch.int32), slot_mapping=torch.arange(6), causal=True)
+    md = tmx.TriangleMixBackend.get_builder_cls()(None, ["l0"], None, "cpu").build(0, common)
+    assert (md.num_actual_tokens, md.max_query_len, md.max_seq_len) == (6, 5, 40)
+    assert md.block_table is common.block_table_tensor and md.has_context is True and md.context_present()
+    common.num_computed_tokens_cpu = torch.tensor([0, 0])
+    common.seq_lens_cpu = torch.tensor([5, 1], dtype=torch.int32)
+    common.max_seq_len = 5
+    assert not tmx.TriangleMixBackend.get_builder_cls()(None, ["l0"], None, "cpu").build(0, common).context_present()
+
+
+def test_layer_selector_feeds_the_analyzer(monkeypatch):
+    from vllm_trianglemix_b200 import layer_selection
+    vals = {0: 3.0, 1: 0.5, 2: 2.0, 3: 0.1}
+    monkeypatch.setattr(layer_selection, "middle_qk_gradient",
+                        lambda q, *a, **k: torch.full((4, 2), -vals[int(q[0, 0, 0])]))
+    sel = tmx.TriangleLayerSelector(4)
+    for layer in range(4):
+        q = torch.full((4, 2, 128), float(layer))
+        sel.observe(layer, q, q, q, q, [4], 0.1)
+    assert sel.select(2) == [1, 3]                                   # lowest mean |gradient|
+    assert sel.to_config(2).triangle_layer_indices == [1, 3]
