@@ -28,7 +28,11 @@ __device__ __forceinline__ void mbar_arrive(uint32_t bar) {
 // try_wait carries a suspend-time hint: the waiting thread sleeps in hardware until the phase completes (or
 // the hint expires) instead of returning after ~60 clk -- without it the waiting producer / issuer warps of the
 // dense kernel spent ~15 % of the kernel's issue slots in this loop (ncu source counts, round 2).
+#ifdef TMX_DEV_NO_SUSPEND_HINT
+constexpr uint32_t kSuspendHintNs = 0u;            // A/B build: the old ~60 clk poll
+#else
 constexpr uint32_t kSuspendHintNs = 1000000u;      // 1 ms
+#endif
 __device__ __forceinline__ void mbar_wait(uint32_t bar, uint32_t parity) {
   uint32_t done = 0;
   for (uint32_t spins = 0; !done; ++spins) {
