@@ -107,9 +107,21 @@ __device__ __forceinline__ uint64_t exp2_poly2(uint64_t t2) {
 // warps have read H1(j) -- before P(j) exists -- and H1(j+1) follows PV(j).  The softmax pass is software-
 // pipelined over its four 32-column chunks.  Each CTA then holds keys {32 rank .. +31} of BOTH halves of the
 // K tile (four 32-key boxes per tile).  Barriers: bH0Full = "H0 ready", bSFull = "H1 ready", bH1Read.
-template <int kEmu, bool kAhead>
-__global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kThreads, 1)
+//
+// kSplit (needs kAhead): TWO threads per query row -- 16 softmax warps per CTA instead of 8.  Warp w serves lane
+// quadrant w & 3 of group (w >> 2) & 1 and HALF h = w >> 3 of every tile: h = 0 the 64 keys of H0, h = 1 those of
+// H1.  The optimistic pass needs no row max, so the two threads of a row only agree on "stale reference?" once per
+// tile (one float through shared memory + a 64-thread named barrier); the rare refresh exchanges the half maxima
+// the same way and each half rescales its own 64 columns of O.  P(j) still lands in H0's block (h writes columns
+// [32h, 32h + 32)), the epilogue splits the 128 output columns.  A warp's pass is half as long and four warps per
+// scheduler hide each other's MUFU / TMEM latencies (the 8-warp pass issues at 0.5 IPC per scheduler).
+constexpr int kThreadsSplit = 576;
+template <int kEmu, bool kAhead, bool kSplit = false>
+__global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kSplit ? kThreadsSplit : kThreads, 1)
 attn_sm100_pair_kernel(const AttnParams p, const __grid_constant__ PairMaps maps) {
+  static_assert(!kSplit || kAhead, "the split softmax builds on the look-ahead schedule");
+  constexpr int kWProd = kSplit ? 16 : 8, kWMma = kSplit ? 17 : 9;     // producer / MMA-issuer warp
+  constexpr int kRing = kSplit ? kStages - 1 : kStages;               // kSplit: the last slot is the exchange area
   extern __shared__ uint8_t smem_raw[];
   const uint32_t smem_base = (ptx::smem_u32(smem_raw) + 1023u) & ~1023u;   // SWIZZLE_128B: 1024-byte atoms
   const uint32_t sQ = smem_base, sRing = smem_base + kOffRing;
@@ -144,27 +156,27 @@ attn_sm100_pair_kernel(const AttnParams p, const __grid_constant__ PairMaps maps
   auto tile_of = [&](int it) { return it < cnt0 ? lo0 + it : lo1 + (it - cnt0); };
 
   // ---- setup -------------------------------------------------------------------
-  if (warp == 8 && lane == 0) {
+  if (warp == kWProd && lane == 0) {
     ptx::prefetch_tmap(&maps.q); ptx::prefetch_tmap(&maps.k); ptx::prefetch_tmap(&maps.v);
     ptx::mbar_init(bar(bQFull), 1);
     for (int s = 0; s < kStages; ++s) { ptx::mbar_init(bar(bFull + s), 1); ptx::mbar_init(bar(bEmpty + s), 1); }
     for (int g = 0; g < 2; ++g) {
       ptx::mbar_init(bar(bSFull + g), 1);
-      ptx::mbar_init(bar(bPReady + g), 8);       // one arrive per softmax warp of the group, both CTAs
+      ptx::mbar_init(bar(bPReady + g), kSplit ? 16 : 8);   // one arrive per softmax warp of the group, both CTAs
       ptx::mbar_init(bar(bOFull + g), 1);
       ptx::mbar_init(bar(bH1Read + g), 8);
       ptx::mbar_init(bar(bH0Full + g), 1);
     }
     ptx::fence_barrier_init();
   }
-  if (warp == 9) ptx::tmem_alloc_pair(sTmemPtr, 512);
+  if (warp == kWMma) ptx::tmem_alloc_pair(sTmemPtr, 512);
   ptx::tc_fence_before();
   ptx::cluster_sync();                            // barriers of BOTH CTAs exist before any remote arrive / TMA
   ptx::tc_fence_after();
   uint32_t tmem_base;
   asm volatile("ld.shared.b32 %0, [%1];" : "=r"(tmem_base) : "r"(sTmemPtr));
 
-  if (warp == 8) {
+  if (warp == kWProd) {
     // =========================== TMA producer (both CTAs) ===========================
     // Item t: even = K(t/2), odd = V(t/2).  This CTA's half: keys [64 rank, 64 rank + 64) of the K tile
     // (both d panels), d panel `rank` of the V tile (all 128 keys).  Bytes are counted on the leader's barrier.
@@ -176,7 +188,7 @@ attn_sm100_pair_kernel(const AttnParams p, const __grid_constant__ PairMaps maps
       const int items = 2 * total;
       int st = 0;
       for (int t = 0; t < items; ++t) {
-        if (t >= kStages) ptx::mbar_wait(bar(bEmpty + st), ((t / kStages) - 1) & 1);
+        if (t >= kRing) ptx::mbar_wait(bar(bEmpty + st), ((t / kRing) - 1) & 1);
         if (leader) ptx::mbar_expect_tx(bar(bFull + st), 2 * kItemBytes);
         const int row = k_start + tile_of(t >> 1) * kBN;
         const uint32_t dst = sRing + st * kItemBytes;
@@ -194,11 +206,11 @@ attn_sm100_pair_kernel(const AttnParams p, const __grid_constant__ PairMaps maps
         } else {
           ptx::tma_load_2d_pair(dst, &maps.v, bar(bFull + st), kvh * kD + 64 * (int)rank, row);
         }
-        if (++st == kStages) st = 0;
+        if (++st == kRing) st = 0;
       }
     }
     __syncwarp();
-  } else if (warp == 9) {
+  } else if (warp == kWMma) {
     // =========================== MMA issuer (leader CTA only) ===========================
     if (leader) {
       const uint32_t tb = __shfl_sync(0xffffffffu, tmem_base, 0);
@@ -256,7 +268,7 @@ attn_sm100_pair_kernel(const AttnParams p, const __grid_constant__ PairMaps maps
       };
 
       int st = 0, ph = 0;                               // ring position of the next item to consume
-      auto advance = [&] { if (++st == kStages) { st = 0; ph ^= 1; } };
+      auto advance = [&] { if (++st == kRing) { st = 0; ph ^= 1; } };
       ptx::mbar_wait_cluster(bar(bQFull), 0);
       ptx::mbar_wait_cluster(bar(bFull + 0), 0);        // K(0)
       ptx::tc_fence_after();
@@ -339,6 +351,197 @@ attn_sm100_pair_kernel(const AttnParams p, const __grid_constant__ PairMaps maps
       }
       }   // !kAhead
     }
+  } else if constexpr (kSplit) {
+    // =========================== softmax, two threads per row (both CTAs) ===========================
+    const int q4 = warp & 3, g = (warp >> 2) & 1, h = warp >> 3;     // lane quadrant, head group, tile half
+    const int i = r0 + q4 * 32 + lane;             // query row inside the sequence
+    const int head = h0 + g;
+    const uint32_t lane_base = (uint32_t)(q4 * 32) << 16;
+    const uint32_t tS = tmem_base + lane_base + kColS + (uint32_t)(g * 128);
+    const uint32_t tO = tmem_base + lane_base + kColO + (uint32_t)(g * 128) + (uint32_t)(h * 64);   // this half's 64 O columns
+    const float sc = p.scale_log2;
+    const uint64_t sc2 = pk_f2(sc, sc);
+    float m_ref = -INFINITY, l_run = 0.f;          // shared reference max (identical in both halves), own partial sum
+    const uint32_t* bm_row = p.bitmask ? p.bitmask + (long long)min(i, n - 1) * p.bitmask_stride : nullptr;
+    // exchange with the other half of the same rows: one float through shared memory (the ring's last slot),
+    // double-buffered, ordered by a 64-thread named barrier
+    const uint32_t sX = sRing + (uint32_t)(kRing * kItemBytes);
+    const int bar_id = 1 + g * 4 + q4;
+    int xc = 0;
+    auto exchange = [&](float mine) -> float {
+      const uint32_t base = sX + (uint32_t)((((xc & 1) * 8 + g * 4 + q4) * 2) * 128) + (uint32_t)(lane * 4);
+      ++xc;
+      asm volatile("st.shared.f32 [%0], %1;" ::"r"(base + (uint32_t)(h * 128)), "f"(mine) : "memory");
+      ptx::named_bar_sync(bar_id, 64);
+      float other;
+      asm volatile("ld.shared.f32 %0, [%1];" : "=f"(other) : "r"(base + (uint32_t)((h ^ 1) * 128)) : "memory");
+      return other;
+    };
+
+    for (int j = 0; j < total; ++j) {
+      const int c0 = tile_of(j) * kBN;
+      const bool full = bm_row == nullptr &&
+                        tile_is_full(r0, r1, c0, c0 + kBN - 1, n, lrow, p.si, p.sl, p.mode);
+      // this half's 64-column block: H0 sits in block j & 1, H1 in the other; P(j) goes to H0's block
+      const uint32_t tH0 = tS + (uint32_t)((j & 1) * 64);
+      const uint32_t tB = tS + (uint32_t)((((j & 1) ^ h)) * 64);
+      auto wait_block = [&]() {
+        ptx::mbar_wait(bar((h == 0 ? bH0Full : bSFull) + g), j & 1);
+        ptx::tc_fence_after();
+      };
+      auto masked = [&](int c, uint32_t (&xr)[32]) {          // chunk c (0 / 1) of this half; PARTIAL tiles only
+        if (!full) {
+          const int cb = c0 + h * 64 + c * 32;
+          const uint32_t bits = bm_row != nullptr ? bm_row[cb >> 5]
+                                                  : mask_word32(i, cb, n, lrow, p.si, p.sl, p.mode);
+#pragma unroll
+          for (int e = 0; e < 32; ++e) xr[e] = ((bits >> e) & 1u) ? xr[e] : 0xff800000u;
+        }
+      };
+      // rare: refresh the shared reference max from the raw scores of BOTH halves, rescale this half's O columns
+      auto refresh = [&]() {
+        ptx::mbar_wait(bar(bSFull + g), j & 1);               // H1(j) complete => PV(j-1) complete (commit order)
+        ptx::tc_fence_after();
+        if (h == 0) wait_block();
+        float mx0 = -INFINITY, mx1 = -INFINITY;
+#pragma unroll
+        for (int c = 0; c < 2; ++c) {
+          uint32_t xr[32];
+          ptx::tmem_ld32(tB + (uint32_t)(c * 32), xr);
+          ptx::tc_wait_ld();
+          masked(c, xr);
+#pragma unroll
+          for (int e = 0; e < 32; e += 4) {
+            mx0 = fmaxf(mx0, fmaxf(__uint_as_float(xr[e]), __uint_as_float(xr[e + 1])));
+            mx1 = fmaxf(mx1, fmaxf(__uint_as_float(xr[e + 2]), __uint_as_float(xr[e + 3])));
+          }
+        }
+        const float mine = fmaxf(mx0, mx1);
+        const float m_new = fmaxf(m_ref, fmaxf(mine, exchange(mine)) * sc);
+        if (j > 0) {
+          const float alpha = (m_new == -INFINITY) ? 1.0f : fast_exp2(m_ref - m_new);   // m_ref = -inf -> 0
+          l_run *= alpha;
+#pragma unroll
+          for (int c = 0; c < 2; ++c) {
+            uint32_t r[32];
+            ptx::tmem_ld32(tO + c * 32, r);
+            ptx::tc_wait_ld();
+#pragma unroll
+            for (int e = 0; e < 32; ++e) r[e] = __float_as_uint(__uint_as_float(r[e]) * alpha);
+            ptx::tmem_st32(tO + c * 32, r);
+          }
+          ptx::tc_wait_st();
+        }
+        m_ref = m_new;
+      };
+      if (__any_sync(0xffffffffu, m_ref == -INFINITY)) refresh();
+      // optimistic pass over this half's 64 scores (no row max; see the 8-warp pass below for the criterion)
+      uint32_t pk[32];             // this half's 64 probabilities as bf16 pairs
+      uint64_t sum2;
+#pragma unroll 1
+      for (int attempt = 0;; ++attempt) {
+        const float neg_m = (m_ref == -INFINITY) ? 0.f : -m_ref;
+        const uint64_t negm2 = pk_f2(neg_m, neg_m);
+        sum2 = pk_f2(0.f, 0.f);
+        auto phase_a = [&](int c, uint32_t (&xr)[32]) {       // raw scores -> t = x * scale - m_ref, in place
+          masked(c, xr);
+#pragma unroll
+          for (int e = 0; e < 32; e += 2) {
+            float a, b;
+            upk_f2(ffma2(pk_f2(__uint_as_float(xr[e]), __uint_as_float(xr[e + 1])), sc2, negm2), a, b);
+            xr[e] = __float_as_uint(a);
+            xr[e + 1] = __float_as_uint(b);
+          }
+        };
+        auto phase_b = [&](int c, const uint32_t (&xr)[32]) { // t -> probabilities, row sum, packed bf16 pairs
+#pragma unroll
+          for (int e = 0; e < 32; e += 2) {
+            float a = __uint_as_float(xr[e]), b = __uint_as_float(xr[e + 1]);
+            uint64_t q2;
+            if ((e & 15) < kEmu) {
+              q2 = exp2_poly2(pk_f2(a, b));
+              upk_f2(q2, a, b);
+            } else {
+              a = fast_exp2(a);
+              b = fast_exp2(b);
+              q2 = pk_f2(a, b);
+            }
+            sum2 = fadd2(sum2, q2);
+            pk[c * 16 + e / 2] = pack2(a, b);
+          }
+        };
+        wait_block();
+        uint32_t b0[32], b1[32];
+        ptx::tmem_ld32(tB, b0);
+        ptx::tc_wait_ld();
+        ptx::tmem_ld32(tB + 32, b1);
+        phase_a(0, b0);
+        ptx::tc_wait_ld();
+        phase_a(1, b1);
+        phase_b(0, b0);
+        float stale = 0.f;
+        if (attempt == 0) {
+          float sa, sb, t0 = -INFINITY, t1 = -INFINITY;
+          upk_f2(sum2, sa, sb);
+#pragma unroll
+          for (int e = 0; e < 32; e += 4) {
+            t0 = fmaxf(t0, fmaxf(__uint_as_float(b1[e]), __uint_as_float(b1[e + 1])));
+            t1 = fmaxf(t1, fmaxf(__uint_as_float(b1[e + 2]), __uint_as_float(b1[e + 3])));
+          }
+          stale = (!(sa + sb <= 128.0f) || fmaxf(t0, t1) > 8.0f) ? 1.f : 0.f;
+          // both threads of a row must take the same decision: every score of the tile is in registers by now
+          stale = fmaxf(stale, exchange(stale));
+        }
+        if (!__any_sync(0xffffffffu, stale != 0.f)) {
+          if (h == 1) {           // H1(j)'s block is read and will not be re-read: the leader may issue H0(j+1) into it
+            ptx::tc_fence_before();
+            __syncwarp();
+            if (lane == 0) ptx::mbar_arrive_leader(bar(bH1Read + g));
+          }
+          phase_b(1, b1);
+          break;
+        }
+        refresh();
+      }
+      {
+        float a, b;
+        upk_f2(sum2, a, b);
+        l_run += a + b;
+      }
+      // bf16 P: keys 64h .. 64h+63 of the tile -> columns [32h, 32h + 32) of H0's block (the other half loaded its
+      // scores from there before the exchange barrier)
+      ptx::tmem_st32(tH0 + (uint32_t)(h * 32), pk);
+      ptx::tc_wait_st();
+      ptx::tc_fence_before();
+      __syncwarp();
+      if (lane == 0) ptx::mbar_arrive_leader(bar(bPReady + g));
+    }
+    // ---- epilogue: this half's 64 columns of O / l -> bf16 -> global ------------------------------
+    ptx::mbar_wait(bar(bOFull + g), 0);
+    ptx::tc_fence_after();
+    const float l_tot = l_run + exchange(l_run);
+    const float inv = l_tot > 0.f ? fast_rcp(l_tot) : 0.f;
+    __nv_bfloat16* orow = p.out + (long long)(seq_start + i) * p.o_stride + head * kD + h * 64;   // seq_start + i = query row
+#pragma unroll
+    for (int c = 0; c < 2; ++c) {
+      uint32_t r[32];
+      ptx::tmem_ld32(tO + c * 32, r);
+      ptx::tc_wait_ld();
+      if (i <= r1) {
+#pragma unroll
+        for (int v4 = 0; v4 < 4; ++v4) {
+          uint4 o;
+          o.x = pack2(__uint_as_float(r[v4 * 8 + 0]) * inv, __uint_as_float(r[v4 * 8 + 1]) * inv);
+          o.y = pack2(__uint_as_float(r[v4 * 8 + 2]) * inv, __uint_as_float(r[v4 * 8 + 3]) * inv);
+          o.z = pack2(__uint_as_float(r[v4 * 8 + 4]) * inv, __uint_as_float(r[v4 * 8 + 5]) * inv);
+          o.w = pack2(__uint_as_float(r[v4 * 8 + 6]) * inv, __uint_as_float(r[v4 * 8 + 7]) * inv);
+          *reinterpret_cast<uint4*>(orow + c * 32 + v4 * 8) = o;
+        }
+      }
+    }
+    if (p.lse != nullptr && h == 0 && i <= r1)
+      p.lse[(long long)head * p.total_T + seq_start + i] = m_ref * 0.6931471805599453f + logf(l_tot);
+    ptx::tc_fence_before();
   } else {
     // =========================== softmax groups (both CTAs) ===========================
     const int g = warp >> 2;                       // 0: head h0, 1: head h0 + 1
@@ -620,7 +823,7 @@ attn_sm100_pair_kernel(const AttnParams p, const __grid_constant__ PairMaps maps
 
   // ---- teardown: neither CTA may leave (or free TMEM) while its peer still reads its memory ----------
   ptx::cluster_sync();
-  if (warp == 9) {
+  if (warp == kWMma) {
     ptx::tc_fence_after();
     ptx::tmem_dealloc_pair(tmem_base, 512);
   }
@@ -640,6 +843,7 @@ int launch_attn_sm100_pair(const AttnParams& p, cudaStream_t s) {
   Kern kern = attn_sm100_pair_kernel<4, true>;
   int slot = kAttrV3Pair;
   bool ahead = true;
+  int threads = kThreads;
 #ifdef TMX_DEV
   // TMX_SM100_VARIANT (developer build): bits 0-1 = exponentials on the FMA pipe per 16 (0, 4, 6, 2 look-ahead / 8 classic),
   // bit 2 = classic schedule (one N = 128 score MMA per tile) instead of look-ahead
@@ -650,6 +854,12 @@ int launch_attn_sm100_pair(const AttnParams& p, cudaStream_t s) {
     static const Kern classic_k[4] = {attn_sm100_pair_kernel<0, false>, attn_sm100_pair_kernel<4, false>,
                                       attn_sm100_pair_kernel<6, false>, attn_sm100_pair_kernel<8, false>};
     if (v != 0) { ahead = (v & 4) == 0; kern = ahead ? ahead_k[v & 3] : classic_k[v & 3]; slot = -1; }
+    // bit 3: two threads per row (16 softmax warps); bits 0-1 pick 0 / 4 / 6 / 2 emulated exponentials per 16
+    if (v & 8) {
+      static const Kern split_k[4] = {attn_sm100_pair_kernel<0, true, true>, attn_sm100_pair_kernel<4, true, true>,
+                                      attn_sm100_pair_kernel<6, true, true>, attn_sm100_pair_kernel<2, true, true>};
+      kern = split_k[v & 3]; ahead = true; threads = kThreadsSplit; slot = -1;
+    }
   }
 #endif
   if (slot < 0) TMX_CUDA_TRY(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, kSmem));
@@ -660,7 +870,7 @@ int launch_attn_sm100_pair(const AttnParams& p, cudaStream_t s) {
   if (st == TMX_OK) st = tma_map_2d(&maps.v, p.v, p.total_kv, (long long)p.Hkv * kD, p.kv_stride, kBN);
   if (st != TMX_OK) return st;
   dim3 grid((unsigned)(2 * p.n_slots), (unsigned)(p.Hq / 4));     // clusters of 2 along x
-  kern<<<grid, kThreads, kSmem, s>>>(p, maps);
+  kern<<<grid, threads, kSmem, s>>>(p, maps);
   count_launch();
   TMX_CUDA_TRY(cudaGetLastError());
   return TMX_OK;
