@@ -391,7 +391,7 @@ attn_sm100_pair_kernel(const AttnParams p, const __grid_constant__ PairMaps maps
       };
       auto masked = [&](int c, uint32_t (&xr)[32]) {          // chunk c (0 / 1) of this half; PARTIAL tiles only
         if (!full) {
-          const int cb = c0 + h * 64 + c * 32;
+          const int cb = pin_in_branch(c0 + h * 64 + c * 32);
           const uint32_t bits = bm_row != nullptr ? bm_row[cb >> 5]
                                                   : mask_word32(i, cb, n, lrow, p.si, p.sl, p.mode);
 #pragma unroll
@@ -571,7 +571,7 @@ attn_sm100_pair_kernel(const AttnParams p, const __grid_constant__ PairMaps maps
         const uint32_t tH1 = tS + (uint32_t)(((j & 1) ^ 1) * 64);
         auto masked = [&](int c, uint32_t (&xr)[32]) {          // apply the mask of chunk c (PARTIAL tiles only)
           if (!full) {
-            const int cb = c0 + c * 32;
+            const int cb = pin_in_branch(c0 + c * 32);
             const uint32_t bits = bm_row != nullptr ? bm_row[cb >> 5]
                                                     : mask_word32(i, cb, n, lrow, p.si, p.sl, p.mode);
 #pragma unroll
@@ -720,7 +720,7 @@ attn_sm100_pair_kernel(const AttnParams p, const __grid_constant__ PairMaps maps
 #pragma unroll
           for (int e = 0; e < 32; ++e) x[e] = __uint_as_float(xr[e]);
           if (!full) {
-            const int cb = c0 + c * 32;
+            const int cb = pin_in_branch(c0 + c * 32);
             const uint32_t bits = bm_row != nullptr ? bm_row[cb >> 5]
                                                     : mask_word32(i, cb, n, lrow, p.si, p.sl, p.mode);
 #pragma unroll

@@ -553,7 +553,7 @@ attn_sm100_v3_kernel(const AttnParams p, const __grid_constant__ TmaMaps maps) {
 #pragma unroll
               for (int e = 0; e < 32; ++e) x[e] = __uint_as_float(xr[e]);
               if (!full) {
-                const int cb = c0 + c * 32;
+                const int cb = pin_in_branch(c0 + c * 32);
                 const uint32_t bits = bm_row != nullptr ? bm_row[cb >> 5]
                                                         : mask_word32(i, cb, n, lrow, p.si, p.sl, p.mode);
 #pragma unroll
@@ -642,7 +642,7 @@ attn_sm100_v3_kernel(const AttnParams p, const __grid_constant__ TmaMaps maps) {
 #pragma unroll
             for (int e = 0; e < 32; ++e) x[e] = __uint_as_float(xr[e]);
             if (!full) {
-              const int cb = c0 + c * 32;
+              const int cb = pin_in_branch(c0 + c * 32);
               const uint32_t bits = bm_row != nullptr ? bm_row[cb >> 5]
                                                       : mask_word32(i, cb, n, lrow, p.si, p.sl, p.mode);
 #pragma unroll
@@ -769,7 +769,7 @@ attn_sm100_v3_kernel(const AttnParams p, const __grid_constant__ TmaMaps maps) {
 #pragma unroll
           for (int e = 0; e < 32; ++e) x[e] = __uint_as_float(xr[e]);
           if (!full) {
-            const int cb = c0 + c * 32;
+            const int cb = pin_in_branch(c0 + c * 32);
             const uint32_t bits = bm_row != nullptr ? bm_row[cb >> 5]
                                                     : mask_word32(i, cb, n, lrow, p.si, p.sl, p.mode);
 #pragma unroll

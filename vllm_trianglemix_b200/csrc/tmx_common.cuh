@@ -74,6 +74,19 @@ __host__ __device__ __forceinline__ uint32_t mask_word32(int i, int c0, int n, i
   return causal & (bit_span32(-c0, shi - c0) | bit_span32(wlo - c0, i - c0));
 }
 
+#ifdef __CUDACC__
+// Keeps the mask arithmetic of PARTIAL tiles inside its branch (`if (!full) { cb = pin_in_branch(...); ... }`):
+// without the opaque value the compiler evaluates the four mask words of EVERY tile speculatively -- ~130 of the
+// ~700 instructions a softmax warp issues per tile (ncu source page of the pair kernel, round 2) although 99.8 %
+// of a dense 128K layer's tiles are full.
+__device__ __forceinline__ int pin_in_branch(int v) {
+#ifndef TMX_DEV_NO_PIN            // developer A/B switch (make DEV=1 DEVEXTRA=-DTMX_DEV_NO_PIN)
+  asm volatile("" : "+r"(v));
+#endif
+  return v;
+}
+#endif
+
 // 32 columns [c0, c0+32) of row i of a piece, as a word (LSB = column c0).
 // Closed form: each row's attended set is a union of at most two intervals.
 __host__ __device__ __forceinline__ uint32_t piece_word(int piece, int i, long long c0,
