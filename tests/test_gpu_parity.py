@@ -278,6 +278,34 @@ def test_attention_peaky_softmax(ops, kernel):
         _check(out.cpu(), ref, ("peaky", mode, kernel))
 
 
+@pytest.mark.parametrize("kernel", KERNELS)
+@pytest.mark.parametrize("step", [3.0, 12.0, -6.0])
+def test_attention_drifting_scores(ops, kernel, step):
+    """Scores that drift by `step` (log2 units) per 128-key tile along the key axis: with a rising drift every tile
+    makes the running reference of the max-free softmax pass stale (the late-refresh path that re-bases the scores
+    it holds in registers); a falling drift leaves the first tile's maximum standing for the whole row."""
+    n, hq, hkv = 2304, 4, 1
+    _skip_unpaired(kernel, hq, hkv)
+    g = torch.Generator().manual_seed(11)
+    u = torch.randn(128, generator=g)
+    u = u / u.norm()
+    ramp = torch.arange(n, dtype=torch.float32) / 128.0 * step / 1.4427          # natural-log units per key
+    k = (torch.randn(n, hkv, 128, generator=g) * 0.5 + (ramp[:, None, None] * u) * (128 ** 0.5) / 4.0).bfloat16()
+    q = (torch.randn(n, hq, 128, generator=g) * 0.5 + 4.0 * u).bfloat16()
+    v = torch.randn(n, hkv, 128, generator=g).bfloat16()
+    cu = torch.tensor([0, n], dtype=torch.int32, device=DEV)
+    for mode, prm in ((0, (0, 0, 0)), (1, (20, 300, 40)), (2, (0, 0, 0))):
+        out = ops.prefill_attn(q.to(DEV), k.to(DEV), v.to(DEV), cu, n, 128 ** -0.5, *prm, mode, kernel=kernel)
+        if mode == 2:       # no mask: plain fp32 softmax(Q K^T * scale) V (ascend_trianglemix.py:86-106 without a mask)
+            kf = k.float().repeat_interleave(hq // hkv, dim=1).transpose(0, 1)
+            vf = v.float().repeat_interleave(hq // hkv, dim=1).transpose(0, 1)
+            w = torch.softmax(torch.matmul(q.float().transpose(0, 1), kf.transpose(-2, -1)) * 128 ** -0.5, dim=-1)
+            ref = torch.matmul(w, vf).transpose(0, 1).contiguous()
+        else:
+            ref = orc.attention_varlen_fp32(q, k, v, [0, n], 128 ** -0.5, *prm, mode)
+        _check(out.cpu(), ref, ("drift", step, mode, kernel))
+
+
 # ------------------------------------------------------------------ seeded fuzz over the whole parameter space
 def _fuzz_case(seed):
     import random

@@ -615,87 +615,143 @@ attn_sm100_pair_kernel(const AttnParams p, const __grid_constant__ PairMaps maps
           }
           m_ref = m_new;
         };
-        if (__any_sync(0xffffffffu, m_ref == -INFINITY)) refresh();
+        if (__builtin_expect(__any_sync(0xffffffffu, m_ref == -INFINITY), 0)) refresh();
         // The optimistic pass: exponentiate against the CURRENT reference without looking for the row max at
         // all (96 FMNMX per row and tile saved).  A stale reference shows up as large probabilities: the pass
         // stands while the row sum of chunks 0-2 stays <= 2^8 and no score of chunk 3 exceeds the reference by
-        // 2^8 (checked where the old kernel knew its max: before H1's block is released and P is stored).
-#pragma unroll 1
-        for (int attempt = 0;; ++attempt) {
-          const float neg_m = (m_ref == -INFINITY) ? 0.f : -m_ref;
-          const uint64_t negm2 = pk_f2(neg_m, neg_m);
-          sum2 = pk_f2(0.f, 0.f);
-          // A: raw scores of chunk c (in xr) -> t = x * scale - m_ref, in place
-          auto phase_a = [&](int c, uint32_t (&xr)[32]) {
-            masked(c, xr);
+        // 2^8 (checked before P is stored).
+        // H1(j)'s column block is handed back to the MMA issuer as soon as its 64 scores sit in registers --
+        // before they are exponentiated and before the stale check (ncu round 2: the softmax warps spent 17 % of
+        // their time waiting for H0 of the NEXT tile, whose issue used to wait for that check).  A stale pass
+        // therefore never re-reads H1 from TMEM: late_refresh() takes chunks 2-3 from registers (t values,
+        // re-based) and re-reads only H0's block, which this warp owns until it stores P there.
+        float neg_m = (m_ref == -INFINITY) ? 0.f : -m_ref;
+        uint64_t negm2 = pk_f2(neg_m, neg_m);
+        sum2 = pk_f2(0.f, 0.f);
+        // A: raw scores of chunk c (in xr) -> t = x * scale - m_ref, in place
+        auto phase_a = [&](int c, uint32_t (&xr)[32]) {
+          masked(c, xr);
 #pragma unroll
-            for (int e = 0; e < 32; e += 2) {
-              float a, b;
-              upk_f2(ffma2(pk_f2(__uint_as_float(xr[e]), __uint_as_float(xr[e + 1])), sc2, negm2), a, b);
-              xr[e] = __float_as_uint(a);
-              xr[e + 1] = __float_as_uint(b);
-            }
-          };
-          // B: t of chunk c (in xr) -> probabilities, row sum, 16 packed bf16 pairs
-          auto phase_b = [&](int c, const uint32_t (&xr)[32]) {
-#pragma unroll
-            for (int e = 0; e < 32; e += 2) {
-              float a = __uint_as_float(xr[e]), b = __uint_as_float(xr[e + 1]);
-              uint64_t q2;
-              if ((e & 15) < kEmu) {
-                q2 = exp2_poly2(pk_f2(a, b));
-                upk_f2(q2, a, b);
-              } else {
-                a = fast_exp2(a);
-                b = fast_exp2(b);
-                q2 = pk_f2(a, b);
-              }
-              sum2 = fadd2(sum2, q2);
-              pk[c * 16 + e / 2] = pack2(a, b);
-            }
-          };
-          uint32_t b0[32], b1[32], b2[32];
-          ptx::tmem_ld32(tH0, b0);
-          ptx::tc_wait_ld();
-          ptx::tmem_ld32(tH0 + 32, b1);
-          phase_a(0, b0);
-          ptx::tc_wait_ld();
-          // everything that only needs H0 first (half of the pass), then wait for keys 64..127
-          phase_a(1, b1);
-          phase_b(0, b0);
-          phase_b(1, b1);
-          ptx::mbar_wait(bar(bSFull + g), j & 1);   // (completed long ago after a refresh)
-          ptx::tc_fence_after();
-          ptx::tmem_ld32(tH1, b2);
-          ptx::tc_wait_ld();
-          ptx::tmem_ld32(tH1 + 32, b0);
-          phase_a(2, b2);
-          ptx::tc_wait_ld();
-          phase_a(3, b0);
-          phase_b(2, b2);
-          bool stale = false;
-          if (attempt == 0) {
-            float sa, sb, t0 = -INFINITY, t1 = -INFINITY;
-            upk_f2(sum2, sa, sb);
-#pragma unroll
-            for (int e = 0; e < 32; e += 4) {
-              t0 = fmaxf(t0, fmaxf(__uint_as_float(b0[e]), __uint_as_float(b0[e + 1])));
-              t1 = fmaxf(t1, fmaxf(__uint_as_float(b0[e + 2]), __uint_as_float(b0[e + 3])));
-            }
-            stale = !(sa + sb <= 256.0f) || fmaxf(t0, t1) > 8.0f;        // (!(<=) also catches NaN / inf)
+          for (int e = 0; e < 32; e += 2) {
+            float a, b;
+            upk_f2(ffma2(pk_f2(__uint_as_float(xr[e]), __uint_as_float(xr[e + 1])), sc2, negm2), a, b);
+            xr[e] = __float_as_uint(a);
+            xr[e + 1] = __float_as_uint(b);
           }
-          if (!__any_sync(0xffffffffu, stale)) {
-            // H1(j)'s block is read and will not be re-read: the leader may issue H0(j+1) into it
-            ptx::tc_fence_before();
-            __syncwarp();
-            if (lane == 0) ptx::mbar_arrive_leader(bar(bH1Read + g));
-            // the first half of P can go out while the last chunk is still being exponentiated
-            ptx::tmem_st32(tH0, *reinterpret_cast<uint32_t(*)[32]>(&pk[0]));
-            phase_b(3, b0);
-            break;
+        };
+        // B: t of chunk c (in xr) -> probabilities, row sum, 16 packed bf16 pairs
+        auto phase_b = [&](int c, const uint32_t (&xr)[32]) {
+#pragma unroll
+          for (int e = 0; e < 32; e += 2) {
+            float a = __uint_as_float(xr[e]), b = __uint_as_float(xr[e + 1]);
+            uint64_t q2;
+            if ((e & 15) < kEmu) {
+              q2 = exp2_poly2(pk_f2(a, b));
+              upk_f2(q2, a, b);
+            } else {
+              a = fast_exp2(a);
+              b = fast_exp2(b);
+              q2 = pk_f2(a, b);
+            }
+            sum2 = fadd2(sum2, q2);
+            pk[c * 16 + e / 2] = pack2(a, b);
           }
-          refresh();
+        };
+        uint32_t b0[32], b1[32], b2[32];
+        ptx::tmem_ld32(tH0, b0);
+        ptx::tc_wait_ld();
+        ptx::tmem_ld32(tH0 + 32, b1);
+        phase_a(0, b0);
+        ptx::tc_wait_ld();
+        // everything that only needs H0 first (half of the pass), then wait for keys 64..127
+        phase_a(1, b1);
+        phase_b(0, b0);
+        phase_b(1, b1);
+        ptx::mbar_wait(bar(bSFull + g), j & 1);   // (completed long ago after a refresh)
+        ptx::tc_fence_after();
+        ptx::tmem_ld32(tH1, b2);
+        ptx::tc_wait_ld();
+        ptx::tmem_ld32(tH1 + 32, b0);
+        phase_a(2, b2);
+        ptx::tc_wait_ld();
+        // H1(j)'s block is read and will not be re-read: the leader may issue H0(j+1) into it
+        ptx::tc_fence_before();
+        __syncwarp();
+        if (lane == 0) ptx::mbar_arrive_leader(bar(bH1Read + g));
+        phase_a(3, b0);
+        phase_b(2, b2);
+        bool stale;
+        {
+          float sa, sb, t0 = -INFINITY, t1 = -INFINITY;
+          upk_f2(sum2, sa, sb);
+#pragma unroll
+          for (int e = 0; e < 32; e += 4) {
+            t0 = fmaxf(t0, fmaxf(__uint_as_float(b0[e]), __uint_as_float(b0[e + 1])));
+            t1 = fmaxf(t1, fmaxf(__uint_as_float(b0[e + 2]), __uint_as_float(b0[e + 3])));
+          }
+          stale = !(sa + sb <= 256.0f) || fmaxf(t0, t1) > 8.0f;        // (!(<=) also catches NaN / inf)
         }
+        if (__builtin_expect(__any_sync(0xffffffffu, stale), 0)) {
+          // late refresh: true row max of this tile = max(raw H0 scores from TMEM, t of chunks 2-3 + old reference)
+          float mx0 = -INFINITY, mx1 = -INFINITY;
+#pragma unroll
+          for (int e = 0; e < 32; e += 2) {
+            mx0 = fmaxf(mx0, fmaxf(__uint_as_float(b2[e]), __uint_as_float(b2[e + 1])));
+            mx1 = fmaxf(mx1, fmaxf(__uint_as_float(b0[e]), __uint_as_float(b0[e + 1])));
+          }
+          float m_new = fmaxf(m_ref, fmaxf(mx0, mx1) - neg_m);      // t = x * scale + neg_m
+#pragma unroll 1
+          for (int c = 0; c < 2; ++c) {
+            ptx::tmem_ld32(tH0 + (uint32_t)(c * 32), b1);
+            ptx::tc_wait_ld();
+            masked(c, b1);
+            float r0_ = -INFINITY, r1_ = -INFINITY;
+#pragma unroll
+            for (int e = 0; e < 32; e += 2) {
+              r0_ = fmaxf(r0_, __uint_as_float(b1[e]));
+              r1_ = fmaxf(r1_, __uint_as_float(b1[e + 1]));
+            }
+            m_new = fmaxf(m_new, fmaxf(r0_, r1_) * sc);
+          }
+          if (j > 0) {
+            // S(j) complete => PV(j-1) complete (commit order); PV(j) waits for our "P ready" below
+            const float alpha = (m_new == -INFINITY) ? 1.0f : fast_exp2(m_ref - m_new);   // m_ref = -inf -> 0
+            l_run *= alpha;
+#pragma unroll 1
+            for (int c = 0; c < 4; ++c) {
+              ptx::tmem_ld32(tO + c * 32, b1);
+              ptx::tc_wait_ld();
+#pragma unroll
+              for (int e = 0; e < 32; ++e) b1[e] = __float_as_uint(__uint_as_float(b1[e]) * alpha);
+              ptx::tmem_st32(tO + c * 32, b1);
+            }
+            ptx::tc_wait_st();
+          }
+          m_ref = m_new;
+          const float neg_new = (m_ref == -INFINITY) ? 0.f : -m_ref;
+          const float delta = neg_new - neg_m;                       // re-base the t values still in registers
+#pragma unroll
+          for (int e = 0; e < 32; ++e) {
+            b2[e] = __float_as_uint(__uint_as_float(b2[e]) + delta);
+            b0[e] = __float_as_uint(__uint_as_float(b0[e]) + delta);
+          }
+          neg_m = neg_new;
+          negm2 = pk_f2(neg_m, neg_m);
+          sum2 = pk_f2(0.f, 0.f);
+          // redo chunks 0-1 from TMEM (one at a time through b1) and chunk 2 from registers
+          ptx::tmem_ld32(tH0, b1);
+          ptx::tc_wait_ld();
+          phase_a(0, b1);
+          phase_b(0, b1);
+          ptx::tmem_ld32(tH0 + 32, b1);
+          ptx::tc_wait_ld();
+          phase_a(1, b1);
+          phase_b(1, b1);
+          phase_b(2, b2);
+        }
+        // the first half of P can go out while the last chunk is still being exponentiated
+        ptx::tmem_st32(tH0, *reinterpret_cast<uint32_t(*)[32]>(&pk[0]));
+        phase_b(3, b0);
         {
           float a, b;
           upk_f2(sum2, a, b);
