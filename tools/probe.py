@@ -6,7 +6,7 @@ import torch
 from vllm_trianglemix_b200 import _lib
 if "--dev" in sys.argv:            # developer library (make DEV=1): honours TMX_SM100_VARIANT
     sys.argv.remove("--dev")
-    _lib.LIB_PATH = os.path.join(os.path.dirname(_lib.LIB_PATH), "libtmx_dev.so")
+    _lib.LIB_PATH = os.path.join(os.path.dirname(_lib.LIB_PATH), os.environ.get("TMX_DEV_LIB", "libtmx_dev.so"))
 from vllm_trianglemix_b200 import ops
 
 

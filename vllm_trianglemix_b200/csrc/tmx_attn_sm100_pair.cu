@@ -122,6 +122,11 @@ attn_sm100_pair_kernel(const AttnParams p, const __grid_constant__ PairMaps maps
   static_assert(!kSplit || kAhead, "the split softmax builds on the look-ahead schedule");
   constexpr int kWProd = kSplit ? 16 : 8, kWMma = kSplit ? 17 : 9;     // producer / MMA-issuer warp
   constexpr int kRing = kSplit ? kStages - 1 : kStages;               // kSplit: the last slot is the exchange area
+#ifdef TMX_DEV_INORDER_ISSUER                                           // developer A/B switch
+  constexpr bool kOoo = false;
+#else
+  constexpr bool kOoo = kAhead && !kSplit && (kStages % 2 == 0);        // polling issuer (ring positions advance by 2)
+#endif
   extern __shared__ uint8_t smem_raw[];
   const uint32_t smem_base = (ptx::smem_u32(smem_raw) + 1023u) & ~1023u;   // SWIZZLE_128B: 1024-byte atoms
   const uint32_t sQ = smem_base, sRing = smem_base + kOffRing;
@@ -159,7 +164,7 @@ attn_sm100_pair_kernel(const AttnParams p, const __grid_constant__ PairMaps maps
   if (warp == kWProd && lane == 0) {
     ptx::prefetch_tmap(&maps.q); ptx::prefetch_tmap(&maps.k); ptx::prefetch_tmap(&maps.v);
     ptx::mbar_init(bar(bQFull), 1);
-    for (int s = 0; s < kStages; ++s) { ptx::mbar_init(bar(bFull + s), 1); ptx::mbar_init(bar(bEmpty + s), 1); }
+    for (int s = 0; s < kStages; ++s) { ptx::mbar_init(bar(bFull + s), 1); ptx::mbar_init(bar(bEmpty + s), kOoo ? 2 : 1); }
     for (int g = 0; g < 2; ++g) {
       ptx::mbar_init(bar(bSFull + g), 1);
       ptx::mbar_init(bar(bPReady + g), kSplit ? 16 : 8);   // one arrive per softmax warp of the group, both CTAs
@@ -272,7 +277,64 @@ attn_sm100_pair_kernel(const AttnParams p, const __grid_constant__ PairMaps maps
       ptx::mbar_wait_cluster(bar(bQFull), 0);
       ptx::mbar_wait_cluster(bar(bFull + 0), 0);        // K(0)
       ptx::tc_fence_after();
-      if constexpr (kAhead) {
+      if constexpr (kOoo) {
+        // Each head group is its own chain  H1 read(j) -> H0(j+1) ... P ready(j) -> PV(j), H1(j+1); the issuer polls
+        // the next barrier of BOTH chains and issues whichever is ready.  (The in-order issuer below could not
+        // issue H0_A(j+1) while it sat waiting for "P ready" of group B, which locked the two groups' softmax
+        // passes to each other: 17 % of the softmax warps' time went into waiting for H0 of their next tile.)
+        // A ring stage is released by one commit per group (count 2), each after the group's last read of it.
+        if (ptx::elect_one()) {
+          for (int g = 0; g < 2; ++g) {
+            issue_s_half(g, 0, 0, 0); ptx::mma_commit_pair(bar(bH0Full + g));
+            issue_s_half(g, 0, 0, 1); ptx::mma_commit_pair(bar(bSFull + g));
+            ptx::mma_commit_pair(bar(bEmpty + 0));
+          }
+        }
+        __syncwarp();
+        // per group: tile j, step (0: H0(j+1) pending, 1: PV(j) pending), ring positions of V(j) and K(j+1)
+        int jg[2] = {0, 0}, step[2] = {0, 0};
+        int vst[2] = {1, 1}, vph[2] = {0, 0}, kst[2] = {2, 2}, kph[2] = {0, 0};
+        int live = ntot > 0 ? 2 : 0;
+        for (uint32_t idle = 0; live > 0; ++idle) {
+          if (idle > (1u << 23)) __trap();                             // ~1 s without progress: a protocol bug, not a wait
+#pragma unroll
+          for (int g = 0; g < 2; ++g) {
+            if (jg[g] >= ntot) continue;
+            const int j = jg[g];
+            const bool more = j + 1 < ntot;
+            if (step[g] == 0) {
+              if (!more) {
+                step[g] = 1;
+              } else if (ptx::mbar_test(bar(bFull + kst[g]), kph[g]) && ptx::mbar_try(bar(bH1Read + g), j & 1)) {
+                ptx::tc_fence_after();
+                if (ptx::elect_one()) { issue_s_half(g, kst[g], j + 1, 0); ptx::mma_commit_pair(bar(bH0Full + g)); }
+                __syncwarp();
+                step[g] = 1;
+              }
+            }
+            if (step[g] == 1 && ptx::mbar_test(bar(bFull + vst[g]), vph[g]) && ptx::mbar_try(bar(bPReady + g), j & 1)) {
+              ptx::tc_fence_after();
+              if (ptx::elect_one()) {
+                issue_pv_blk(g, vst[g], j > 0, j);
+                if (!more) ptx::mma_commit_pair(bar(bOFull + g));
+                ptx::mma_commit_pair(bar(bEmpty + vst[g]));
+                if (more) {
+                  issue_s_half(g, kst[g], j + 1, 1);                   // into P(j)'s block, behind PV(j)
+                  ptx::mma_commit_pair(bar(bSFull + g));
+                  ptx::mma_commit_pair(bar(bEmpty + kst[g]));
+                }
+              }
+              __syncwarp();
+              // next tile: V(j+1) and K(j+2) sit two ring items further
+              vst[g] += 2; if (vst[g] >= kRing) { vst[g] -= kRing; vph[g] ^= 1; }
+              kst[g] += 2; if (kst[g] >= kRing) { kst[g] -= kRing; kph[g] ^= 1; }
+              step[g] = 0;
+              idle = 0;
+              if (++jg[g] == ntot) --live;
+            }
+          }
+        }
+      } else if constexpr (kAhead) {
         if (ptx::elect_one()) {
           for (int g = 0; g < 2; ++g) {
             issue_s_half(g, 0, 0, 0); ptx::mma_commit_pair(bar(bH0Full + g));
@@ -645,7 +707,7 @@ attn_sm100_pair_kernel(const AttnParams p, const __grid_constant__ PairMaps maps
           for (int e = 0; e < 32; e += 2) {
             float a = __uint_as_float(xr[e]), b = __uint_as_float(xr[e + 1]);
             uint64_t q2;
-            if ((e & 15) < kEmu) {
+            if ((((e >> 1) * (kEmu / 2)) & 7) < kEmu / 2) {        // kEmu of every 16, spread evenly over the pairs
               q2 = exp2_poly2(pk_f2(a, b));
               upk_f2(q2, a, b);
             } else {

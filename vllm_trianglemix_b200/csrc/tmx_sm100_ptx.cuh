@@ -45,7 +45,6 @@ __device__ __forceinline__ void mbar_wait(uint32_t bar, uint32_t parity) {
   }
 }
 
-// One lane of a converged warp (always the same one); keeps the enclosing control flow warp-uniform.
 // non-blocking: has the phase with this parity completed?
 __device__ __forceinline__ bool mbar_test(uint32_t bar, uint32_t parity) {
   uint32_t done;
@@ -57,6 +56,19 @@ __device__ __forceinline__ bool mbar_test(uint32_t bar, uint32_t parity) {
   return done != 0;
 }
 
+// one potentially-blocking poll without a suspend-time hint: returns after the phase completes or after the
+// hardware's default time limit (~60 clk on sm_100), whichever comes first
+__device__ __forceinline__ bool mbar_try(uint32_t bar, uint32_t parity) {
+  uint32_t done;
+  asm volatile(
+      "{\n.reg .pred p;\n"
+      "mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n"
+      "selp.u32 %0, 1, 0, p;\n}"
+      : "=r"(done) : "r"(bar), "r"(parity) : "memory");
+  return done != 0;
+}
+
+// One lane of a converged warp (always the same one); keeps the enclosing control flow warp-uniform.
 __device__ __forceinline__ bool elect_one() {
   uint32_t pred;
   asm volatile(
