@@ -53,6 +53,20 @@ static_assert(kSmem <= 232448, "exceeds the 227 KB of shared memory a CTA may us
 constexpr uint32_t kColS = 0;      // + g * 128
 constexpr uint32_t kColO = 256;    // + g * 128
 
+// Developer build: clock64 timeline of the first 96 KV tiles of cluster 1's leader CTA (cluster 0 takes the padding slot of a one-sequence batch) (tools/pair_trace.py).
+// Events: 0-3 group A (warp 0): H0 seen, H1 seen, "H1 read" arrived, "P ready" arrived; issuer: 4 saw "H1 read" of A,
+// 5 saw "P ready" of A, 6 PV_A(t) issued (before H1_A(t+1)); 8-11 H0_A(t+1), PV_A(t) + H1_A(t+1), H0_B(t+1), PV_B(t) +
+// H1_B(t+1) issued.
+#ifdef TMX_DEV
+#define PAIR_TRACE(ev, t)                                                                                   \
+  do {                                                                                                      \
+    if (p.trace != nullptr && blockIdx.x == 2 && blockIdx.y == 0 && (t) < 96 && lane == 0)                  \
+      p.trace[(long long)(t) * 12 + (ev)] = clock64();                                                      \
+  } while (0)
+#else
+#define PAIR_TRACE(ev, t) do { } while (0)
+#endif
+
 struct PairMaps {
   CUtensorMap q, k, v;             // boxes: 128 rows (q), 64 rows (k half), 128 rows (v half)
 };
@@ -283,6 +297,9 @@ attn_sm100_pair_kernel(const AttnParams p, const __grid_constant__ PairMaps maps
         // issue H0_A(j+1) while it sat waiting for "P ready" of group B, which locked the two groups' softmax
         // passes to each other: 17 % of the softmax warps' time went into waiting for H0 of their next tile.)
         // A ring stage is released by one commit per group (count 2), each after the group's last read of it.
+        // The polls are try_waits without a time hint (they return within ~100 clk): tight test_wait polling reacts no
+        // faster in practice -- the issuer blocks in the tcgen05 queue most of the time anyway (27 clk per MMA issued,
+        // tools/pair_trace.py) -- and takes issue slots from the two softmax warps of its scheduler (1240 vs 1250).
         if (ptx::elect_one()) {
           for (int g = 0; g < 2; ++g) {
             issue_s_half(g, 0, 0, 0); ptx::mma_commit_pair(bar(bH0Full + g));
@@ -307,17 +324,23 @@ attn_sm100_pair_kernel(const AttnParams p, const __grid_constant__ PairMaps maps
                 step[g] = 1;
               } else if (ptx::mbar_test(bar(bFull + kst[g]), kph[g]) && ptx::mbar_try(bar(bH1Read + g), j & 1)) {
                 ptx::tc_fence_after();
+                if (g == 0) PAIR_TRACE(4, j);
                 if (ptx::elect_one()) { issue_s_half(g, kst[g], j + 1, 0); ptx::mma_commit_pair(bar(bH0Full + g)); }
                 __syncwarp();
+                PAIR_TRACE(8 + 2 * g, j);
                 step[g] = 1;
               }
             }
             if (step[g] == 1 && ptx::mbar_test(bar(bFull + vst[g]), vph[g]) && ptx::mbar_try(bar(bPReady + g), j & 1)) {
               ptx::tc_fence_after();
+              if (g == 0) PAIR_TRACE(5, j);
               if (ptx::elect_one()) {
                 issue_pv_blk(g, vst[g], j > 0, j);
                 if (!more) ptx::mma_commit_pair(bar(bOFull + g));
                 ptx::mma_commit_pair(bar(bEmpty + vst[g]));
+#ifdef TMX_DEV
+                if (g == 0 && p.trace != nullptr && blockIdx.x == 2 && blockIdx.y == 0 && j < 96) p.trace[(long long)j * 12 + 6] = clock64();
+#endif
                 if (more) {
                   issue_s_half(g, kst[g], j + 1, 1);                   // into P(j)'s block, behind PV(j)
                   ptx::mma_commit_pair(bar(bSFull + g));
@@ -325,6 +348,7 @@ attn_sm100_pair_kernel(const AttnParams p, const __grid_constant__ PairMaps maps
                 }
               }
               __syncwarp();
+              PAIR_TRACE(9 + 2 * g, j);
               // next tile: V(j+1) and K(j+2) sit two ring items further
               vst[g] += 2; if (vst[g] >= kRing) { vst[g] -= kRing; vph[g] ^= 1; }
               kst[g] += 2; if (kst[g] >= kRing) { kst[g] -= kRing; kph[g] ^= 1; }
@@ -621,6 +645,7 @@ attn_sm100_pair_kernel(const AttnParams p, const __grid_constant__ PairMaps maps
     for (int j = 0; j < total; ++j) {
       if constexpr (kAhead) ptx::mbar_wait(bar(bH0Full + g), j & 1);          // first 64 keys of S(j)
       else ptx::mbar_wait(bar(bSFull + g), j & 1);
+      if (warp == 0) { PAIR_TRACE(0, j); }
       ptx::tc_fence_after();
       const int c0 = tile_of(j) * kBN;
       const bool full = bm_row == nullptr &&
@@ -730,6 +755,7 @@ attn_sm100_pair_kernel(const AttnParams p, const __grid_constant__ PairMaps maps
         phase_b(0, b0);
         phase_b(1, b1);
         ptx::mbar_wait(bar(bSFull + g), j & 1);   // (completed long ago after a refresh)
+        if (warp == 0) { PAIR_TRACE(1, j); }
         ptx::tc_fence_after();
         ptx::tmem_ld32(tH1, b2);
         ptx::tc_wait_ld();
@@ -740,6 +766,7 @@ attn_sm100_pair_kernel(const AttnParams p, const __grid_constant__ PairMaps maps
         ptx::tc_fence_before();
         __syncwarp();
         if (lane == 0) ptx::mbar_arrive_leader(bar(bH1Read + g));
+        if (warp == 0) { PAIR_TRACE(2, j); }
         phase_a(3, b0);
         phase_b(2, b2);
         bool stale;
@@ -824,6 +851,7 @@ attn_sm100_pair_kernel(const AttnParams p, const __grid_constant__ PairMaps maps
         ptx::tc_fence_before();
         __syncwarp();
         if (lane == 0) ptx::mbar_arrive_leader(bar(bPReady + g));
+        if (warp == 0) { PAIR_TRACE(3, j); }
         continue;
       }
 #pragma unroll 1
