@@ -12,7 +12,7 @@ from vllm_trianglemix_b200 import _lib
 _lib.LIB_PATH = os.path.join(os.path.dirname(_lib.LIB_PATH), os.environ.get("TMX_DEV_LIB", "libtmx_dev.so"))
 from vllm_trianglemix_b200 import ops  # noqa: E402
 
-EV = ["A H0 seen", "A H1 seen", "A H1 read", "A P ready", "iss saw H1rd", "iss saw Prdy", "PV_A issued", "-",
+EV = ["w0 H0 seen", "w1 H0 seen", "w2 H0 seen", "w3 H0 seen", "w0 P ready", "w1 P ready", "w2 P ready", "w3 P ready",
       "H0_A(t+1) iss", "H1_A(t+1) iss", "H0_B(t+1) iss", "H1_B(t+1) iss"]
 
 
@@ -42,13 +42,14 @@ def main():
     period = (t[-1, 0] - t[0, 0]) / (t.shape[0] - 1)
     print("tile period (group A, H0 seen -> H0 seen): %.0f clk  => tensor pipe %.1f %% of the 2048-clk MMA time" %
           (period, 100 * 2048 / period))
-    d = lambda a, b: (t[:, b] - t[:, a]).mean()
-    print("group A: H0 seen -> H1 seen %5.0f | H1 seen -> H1 read %5.0f | H1 read -> P ready %5.0f | P ready -> next H0 seen "
-          "%5.0f" % (d(0, 1), d(1, 2), d(2, 3), (t[1:, 0] - t[:-1, 3]).mean()))
-    print("issuer : H1 read arrived -> seen %5.0f -> H0_A(t+1) issued %5.0f | P ready arrived -> seen %5.0f -> PV_A issued "
-          "%5.0f -> H1_A(t+1) issued %5.0f" % (d(2, 4), d(4, 8), d(3, 5), d(5, 6), d(6, 9)))
-    print("tensor : H0_A(t+1) issued -> A H0 seen(t+1) %5.0f | PV_A(t) issued -> A H1 seen(t+1) %5.0f | H1_A(t+1) issued -> "
-          "seen %5.0f" % ((t[1:, 0] - t[:-1, 8]).mean(), (t[1:, 1] - t[:-1, 6]).mean(), (t[1:, 1] - t[:-1, 9]).mean()))
+    for w in range(4):
+        print("warp %d (scheduler %d): pass H0 seen -> P ready %5.0f | P ready -> next H0 seen %5.0f | P ready behind the "
+              "first warp's %5.0f" % (w, w, (t[:, 4 + w] - t[:, w]).mean(), (t[1:, w] - t[:-1, 4 + w]).mean(),
+                                      (t[:, 4 + w] - t[:, 4:8].min(dim=1).values).mean()))
+    last = t[:, 4:8].argmax(dim=1)
+    print("last warp to arrive at 'P ready': " + ", ".join("warp %d: %d tiles" % (w, int((last == w).sum())) for w in range(4)))
+    print("last P ready -> PV_A + H1_A(t+1) issued %5.0f | H0_A(t+1) issued -> first H0 seen(t+1) %5.0f" %
+          ((t[:, 9] - t[:, 4:8].max(dim=1).values).mean(), (t[1:, 0:4].min(dim=1).values - t[:-1, 8]).mean()))
     base = tr[40, 0]
     print("raw tiles 40..45 relative to tile 40's 'A H0 seen':")
     print("   " + " ".join("%13s" % e for e in EV))

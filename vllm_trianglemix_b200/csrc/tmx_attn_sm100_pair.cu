@@ -30,7 +30,7 @@ namespace {
 constexpr int kD = 128;
 constexpr int kBM = 128;
 constexpr int kBN = 128;
-constexpr int kThreads = 320;
+constexpr int kThreads = 352;                    // 8 softmax warps, producer, two MMA issuers (one per head group)
 constexpr int kQBytes = 2 * 2 * kBM * 128;        // 2 heads x 2 panels of [128 rows][64 d] = 64 KB per CTA
 constexpr int kKPanel = (kBN / 2) * 128;          // this CTA's 64 keys x 64 d = 8 KB
 constexpr int kItemBytes = 2 * kKPanel;           // K half (64 keys x 128 d) or V half (128 keys x 64 d): 16 KB
@@ -53,10 +53,9 @@ static_assert(kSmem <= 232448, "exceeds the 227 KB of shared memory a CTA may us
 constexpr uint32_t kColS = 0;      // + g * 128
 constexpr uint32_t kColO = 256;    // + g * 128
 
-// Developer build: clock64 timeline of the first 96 KV tiles of cluster 1's leader CTA (cluster 0 takes the padding slot of a one-sequence batch) (tools/pair_trace.py).
-// Events: 0-3 group A (warp 0): H0 seen, H1 seen, "H1 read" arrived, "P ready" arrived; issuer: 4 saw "H1 read" of A,
-// 5 saw "P ready" of A, 6 PV_A(t) issued (before H1_A(t+1)); 8-11 H0_A(t+1), PV_A(t) + H1_A(t+1), H0_B(t+1), PV_B(t) +
-// H1_B(t+1) issued.
+// Developer build: clock64 timeline of the first 96 KV tiles of cluster 1's leader CTA (cluster 0 takes the padding
+// slot of a one-sequence batch); tools/pair_trace.py.  Events: 0-3 "H0 seen" of group A's warps 0-3 (one per scheduler),
+// 4-7 their "P ready" arrives; issuers: 8-11 H0_A(t+1), PV_A(t) + H1_A(t+1), H0_B(t+1), PV_B(t) + H1_B(t+1) issued.
 #ifdef TMX_DEV
 #define PAIR_TRACE(ev, t)                                                                                   \
   do {                                                                                                      \
@@ -139,7 +138,7 @@ attn_sm100_pair_kernel(const AttnParams p, const __grid_constant__ PairMaps maps
 #ifdef TMX_DEV_INORDER_ISSUER                                           // developer A/B switch
   constexpr bool kOoo = false;
 #else
-  constexpr bool kOoo = kAhead && !kSplit && (kStages % 2 == 0);        // polling issuer (ring positions advance by 2)
+  constexpr bool kOoo = kAhead && !kSplit && (kStages % 2 == 0);        // one issuer warp per head group (ring positions advance by 2)
 #endif
   extern __shared__ uint8_t smem_raw[];
   const uint32_t smem_base = (ptx::smem_u32(smem_raw) + 1023u) & ~1023u;   // SWIZZLE_128B: 1024-byte atoms
@@ -229,8 +228,8 @@ attn_sm100_pair_kernel(const AttnParams p, const __grid_constant__ PairMaps maps
       }
     }
     __syncwarp();
-  } else if (warp == kWMma) {
-    // =========================== MMA issuer (leader CTA only) ===========================
+  } else if (warp == kWMma || (kOoo && warp == kWMma + 1)) {
+    // =========================== MMA issuer(s) (leader CTA only) ===========================
     if (leader) {
       const uint32_t tb = __shfl_sync(0xffffffffu, tmem_base, 0);
       const int ntot = __shfl_sync(0xffffffffu, total, 0);
@@ -292,71 +291,50 @@ attn_sm100_pair_kernel(const AttnParams p, const __grid_constant__ PairMaps maps
       ptx::mbar_wait_cluster(bar(bFull + 0), 0);        // K(0)
       ptx::tc_fence_after();
       if constexpr (kOoo) {
-        // Each head group is its own chain  H1 read(j) -> H0(j+1) ... P ready(j) -> PV(j), H1(j+1); the issuer polls
-        // the next barrier of BOTH chains and issues whichever is ready.  (The in-order issuer below could not
-        // issue H0_A(j+1) while it sat waiting for "P ready" of group B, which locked the two groups' softmax
-        // passes to each other: 17 % of the softmax warps' time went into waiting for H0 of their next tile.)
-        // A ring stage is released by one commit per group (count 2), each after the group's last read of it.
-        // The polls are try_waits without a time hint (they return within ~100 clk): tight test_wait polling reacts no
-        // faster in practice -- the issuer blocks in the tcgen05 queue most of the time anyway (27 clk per MMA issued,
-        // tools/pair_trace.py) -- and takes issue slots from the two softmax warps of its scheduler (1240 vs 1250).
+        // One issuer WARP per head group (warp kWMma: group A, kWMma + 1: group B), each walking its own chain
+        //   "H1 read"(j) -> H0(j+1) ... "P ready"(j) -> PV(j), H1(j+1)
+        // with sleeping mbarrier waits.  History (profiles/r02_pair_kernel.md): a single in-order issuer could not
+        // issue H0_A(j+1) while it waited for "P ready" of group B, which locked the two groups' softmax passes to
+        // each other; a single POLLING issuer fixed that (+1.2 %) but its poll loop took issue slots from the two
+        // softmax warps of its scheduler -- clock64 trace: warp 1 arrived 900 clk after warps 0, 2, 3 at every
+        // "P ready", and the M = 256 MMAs wait for the slowest of the 8 warps.  tcgen05 operations of different
+        // threads are unordered, which is fine here: the groups share no TMEM columns, and a ring stage is
+        // released by one commit per group (count 2), each after that group's last read of it.
+        const int g = warp - kWMma;
         if (ptx::elect_one()) {
-          for (int g = 0; g < 2; ++g) {
-            issue_s_half(g, 0, 0, 0); ptx::mma_commit_pair(bar(bH0Full + g));
-            issue_s_half(g, 0, 0, 1); ptx::mma_commit_pair(bar(bSFull + g));
-            ptx::mma_commit_pair(bar(bEmpty + 0));
-          }
+          issue_s_half(g, 0, 0, 0); ptx::mma_commit_pair(bar(bH0Full + g));
+          issue_s_half(g, 0, 0, 1); ptx::mma_commit_pair(bar(bSFull + g));
+          ptx::mma_commit_pair(bar(bEmpty + 0));
         }
         __syncwarp();
-        // per group: tile j, step (0: H0(j+1) pending, 1: PV(j) pending), ring positions of V(j) and K(j+1)
-        int jg[2] = {0, 0}, step[2] = {0, 0};
-        int vst[2] = {1, 1}, vph[2] = {0, 0}, kst[2] = {2, 2}, kph[2] = {0, 0};
-        int live = ntot > 0 ? 2 : 0;
-        for (uint32_t idle = 0; live > 0; ++idle) {
-          if (idle > (1u << 23)) __trap();                             // ~1 s without progress: a protocol bug, not a wait
-#pragma unroll
-          for (int g = 0; g < 2; ++g) {
-            if (jg[g] >= ntot) continue;
-            const int j = jg[g];
-            const bool more = j + 1 < ntot;
-            if (step[g] == 0) {
-              if (!more) {
-                step[g] = 1;
-              } else if (ptx::mbar_test(bar(bFull + kst[g]), kph[g]) && ptx::mbar_try(bar(bH1Read + g), j & 1)) {
-                ptx::tc_fence_after();
-                if (g == 0) PAIR_TRACE(4, j);
-                if (ptx::elect_one()) { issue_s_half(g, kst[g], j + 1, 0); ptx::mma_commit_pair(bar(bH0Full + g)); }
-                __syncwarp();
-                PAIR_TRACE(8 + 2 * g, j);
-                step[g] = 1;
-              }
-            }
-            if (step[g] == 1 && ptx::mbar_test(bar(bFull + vst[g]), vph[g]) && ptx::mbar_try(bar(bPReady + g), j & 1)) {
-              ptx::tc_fence_after();
-              if (g == 0) PAIR_TRACE(5, j);
-              if (ptx::elect_one()) {
-                issue_pv_blk(g, vst[g], j > 0, j);
-                if (!more) ptx::mma_commit_pair(bar(bOFull + g));
-                ptx::mma_commit_pair(bar(bEmpty + vst[g]));
-#ifdef TMX_DEV
-                if (g == 0 && p.trace != nullptr && blockIdx.x == 2 && blockIdx.y == 0 && j < 96) p.trace[(long long)j * 12 + 6] = clock64();
-#endif
-                if (more) {
-                  issue_s_half(g, kst[g], j + 1, 1);                   // into P(j)'s block, behind PV(j)
-                  ptx::mma_commit_pair(bar(bSFull + g));
-                  ptx::mma_commit_pair(bar(bEmpty + kst[g]));
-                }
-              }
-              __syncwarp();
-              PAIR_TRACE(9 + 2 * g, j);
-              // next tile: V(j+1) and K(j+2) sit two ring items further
-              vst[g] += 2; if (vst[g] >= kRing) { vst[g] -= kRing; vph[g] ^= 1; }
-              kst[g] += 2; if (kst[g] >= kRing) { kst[g] -= kRing; kph[g] ^= 1; }
-              step[g] = 0;
-              idle = 0;
-              if (++jg[g] == ntot) --live;
+        int vst = 1, vph = 0, kst = 2, kph = 0;          // ring positions of V(j) and K(j+1): items 2j+1 and 2j+2
+        for (int j = 0; j < ntot; ++j) {
+          const bool more = j + 1 < ntot;
+          if (more) {
+            ptx::mbar_wait_cluster(bar(bFull + kst), kph);
+            ptx::mbar_wait_cluster(bar(bH1Read + g), j & 1);         // H1(j)'s block has been read (both CTAs)
+            ptx::tc_fence_after();
+            if (ptx::elect_one()) { issue_s_half(g, kst, j + 1, 0); ptx::mma_commit_pair(bar(bH0Full + g)); }
+            __syncwarp();
+            PAIR_TRACE(8 + 2 * g, j);
+          }
+          ptx::mbar_wait_cluster(bar(bFull + vst), vph);
+          ptx::mbar_wait_cluster(bar(bPReady + g), j & 1);
+          ptx::tc_fence_after();
+          if (ptx::elect_one()) {
+            issue_pv_blk(g, vst, j > 0, j);
+            if (!more) ptx::mma_commit_pair(bar(bOFull + g));
+            ptx::mma_commit_pair(bar(bEmpty + vst));
+            if (more) {
+              issue_s_half(g, kst, j + 1, 1);                        // into P(j)'s block, behind PV(j)
+              ptx::mma_commit_pair(bar(bSFull + g));
+              ptx::mma_commit_pair(bar(bEmpty + kst));
             }
           }
+          __syncwarp();
+          PAIR_TRACE(9 + 2 * g, j);
+          vst += 2; if (vst >= kRing) { vst -= kRing; vph ^= 1; }
+          kst += 2; if (kst >= kRing) { kst -= kRing; kph ^= 1; }
         }
       } else if constexpr (kAhead) {
         if (ptx::elect_one()) {
@@ -628,6 +606,8 @@ attn_sm100_pair_kernel(const AttnParams p, const __grid_constant__ PairMaps maps
     if (p.lse != nullptr && h == 0 && i <= r1)
       p.lse[(long long)head * p.total_T + seq_start + i] = m_ref * 0.6931471805599453f + logf(l_tot);
     ptx::tc_fence_before();
+  } else if (!kSplit && warp >= 8) {
+    // (the second issuer warp of a variant with ONE issuer, and both issuer warps of the peer CTA: nothing to do)
   } else {
     // =========================== softmax groups (both CTAs) ===========================
     const int g = warp >> 2;                       // 0: head h0, 1: head h0 + 1
@@ -645,7 +625,7 @@ attn_sm100_pair_kernel(const AttnParams p, const __grid_constant__ PairMaps maps
     for (int j = 0; j < total; ++j) {
       if constexpr (kAhead) ptx::mbar_wait(bar(bH0Full + g), j & 1);          // first 64 keys of S(j)
       else ptx::mbar_wait(bar(bSFull + g), j & 1);
-      if (warp == 0) { PAIR_TRACE(0, j); }
+      if (warp < 4) { PAIR_TRACE(warp, j); }
       ptx::tc_fence_after();
       const int c0 = tile_of(j) * kBN;
       const bool full = bm_row == nullptr &&
@@ -755,7 +735,6 @@ attn_sm100_pair_kernel(const AttnParams p, const __grid_constant__ PairMaps maps
         phase_b(0, b0);
         phase_b(1, b1);
         ptx::mbar_wait(bar(bSFull + g), j & 1);   // (completed long ago after a refresh)
-        if (warp == 0) { PAIR_TRACE(1, j); }
         ptx::tc_fence_after();
         ptx::tmem_ld32(tH1, b2);
         ptx::tc_wait_ld();
@@ -766,7 +745,6 @@ attn_sm100_pair_kernel(const AttnParams p, const __grid_constant__ PairMaps maps
         ptx::tc_fence_before();
         __syncwarp();
         if (lane == 0) ptx::mbar_arrive_leader(bar(bH1Read + g));
-        if (warp == 0) { PAIR_TRACE(2, j); }
         phase_a(3, b0);
         phase_b(2, b2);
         bool stale;
@@ -851,7 +829,7 @@ attn_sm100_pair_kernel(const AttnParams p, const __grid_constant__ PairMaps maps
         ptx::tc_fence_before();
         __syncwarp();
         if (lane == 0) ptx::mbar_arrive_leader(bar(bPReady + g));
-        if (warp == 0) { PAIR_TRACE(3, j); }
+        if (warp < 4) { PAIR_TRACE(4 + warp, j); }
         continue;
       }
 #pragma unroll 1
