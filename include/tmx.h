@@ -43,7 +43,9 @@ typedef enum {
   TMX_ERR_WORKSPACE = 4,    /* workspace null or smaller than tmx_attn_workspace_bytes */
   TMX_ERR_ARCH = 5,         /* device is not compute capability 10.x            */
   TMX_ERR_CUDA = 6,         /* a CUDA runtime/driver call failed (see tmx_last_cuda_error) */
-  TMX_ERR_UNSUPPORTED = 7   /* valid request this build cannot serve            */
+  TMX_ERR_UNSUPPORTED = 7,  /* valid request this build cannot serve            */
+  TMX_ERR_STATIC_SCRATCH = 8 /* tmx_prefill_attn_static: the request needs more scratch than
+                                TMX_STATIC_SCRATCH_BYTES -- use tmx_prefill_attn with a caller workspace */
 } tmx_status;
 
 /* mask_mode of a layer: the output of should_use_triangle()
@@ -152,6 +154,29 @@ int tmx_prefill_attn(void* out, const void* q, const void* k, const void* v,
                      int mode, const uint32_t* bitmask, int64_t bitmask_stride_words,
                      float* lse, void* workspace, size_t workspace_bytes, int kernel,
                      tmx_stream_t stream);
+
+/* ---- allocation-free variant of tmx_prefill_attn ---------------------------------------
+ * No counterpart in the reference: added for callers that cannot call
+ * cudaMalloc (code under CUDA graph capture, tight serving loops, harnesses that forbid it).
+ * Same arguments, checks, kernels and results as tmx_prefill_attn, minus (workspace, workspace_bytes): the scratch
+ * (block index + split-KV partials) is a file-scope `static __device__` array of TMX_STATIC_SCRATCH_BYTES inside the
+ * library -- every GPU that loads libtmx.so holds those bytes until the process exits.  The call allocates nothing:
+ * no cudaMalloc / cudaFree / allocating library routine; its one-time set-up per device is a cudaGetSymbolAddress.
+ * The caller still passes q / k / v / cu_seqlens / out (/ lse / bitmask).
+ * Limit: a request whose tmx_attn_workspace_bytes() exceeds TMX_STATIC_SCRATCH_BYTES returns TMX_ERR_STATIC_SCRATCH
+ * and launches nothing (every dense-causal layer and every TMX_KERNEL_TCGEN05 / _PAIR request fits at any length: their
+ * scratch is the block index, 32 KB at 128K tokens; a TMX_KERNEL_AUTO triangle layer -- split-KV partials of the dense
+ * tail rows -- fits up to about 16K tokens of Qwen3-8B shape, 130 MB at 128K does not).
+ * Sharing: every call on a device uses the SAME array, which keeps the last call's contents; each call rewrites
+ * what it reads (the block index is cleared by the call itself), so nothing has to be zeroed by the caller.  Calls
+ * that overlap on the GPU (two streams, two threads) RACE on the array: serialise them, or use tmx_prefill_attn. */
+#define TMX_STATIC_SCRATCH_BYTES (16u << 20)
+int tmx_prefill_attn_static(void* out, const void* q, const void* k, const void* v,
+                            const int32_t* cu_seqlens, int B, int total_T, int max_seqlen,
+                            int Hq, int Hkv, int D, int64_t q_stride_t, int64_t kv_stride_t,
+                            int64_t o_stride_t, float scale, int si, int sl, int last,
+                            int mode, const uint32_t* bitmask, int64_t bitmask_stride_words,
+                            float* lse, int kernel, tmx_stream_t stream);
 
 /* ---- chunked prefill / prefix context / decode over the KV cache ----
  * The same attention when the call's query rows are only the TAIL of each sequence: sequence b

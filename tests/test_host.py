@@ -74,7 +74,7 @@ def test_status_strings_and_version():
     lib = _lib.load()
     assert lib.tmx_version() >= 100
     seen = set()
-    for code in range(0, 8):
+    for code in range(0, 9):
         s = lib.tmx_strerror(code).decode()
         assert s and s not in seen
         seen.add(s)

@@ -29,6 +29,9 @@ SIGNATURES = {
     "tmx_prefill_attn": (_i32, [_vp, _vp, _vp, _vp, _vp, _i32, _i32, _i32, _i32, _i32, _i32,
                                 _i64, _i64, _i64, _f32, _i32, _i32, _i32, _i32, _vp, _i64,
                                 _vp, _vp, _sz, _i32, _vp]),
+    "tmx_prefill_attn_static": (_i32, [_vp, _vp, _vp, _vp, _vp, _i32, _i32, _i32, _i32, _i32, _i32,
+                                       _i64, _i64, _i64, _f32, _i32, _i32, _i32, _i32, _vp, _i64,
+                                       _vp, _i32, _vp]),
     "tmx_chunked_prefill_attn": (_i32, [_vp, _vp, _vp, _vp, _i32, _i32, _i32, _i32, _i32, _i32, _i64, _i64,
                                         _vp, _vp, _i64, _i64, _vp, _vp, _i64, _i32, _f32, _i32, _i32, _i32,
                                         _i32, _vp, _vp, _sz, _i32, _vp]),

@@ -209,6 +209,9 @@ extern "C" const char* tmx_strerror(int status) {
     case TMX_ERR_ARCH: return "device is not compute capability 10.x (B200, sm_100a)";
     case TMX_ERR_CUDA: return "CUDA call failed (see tmx_last_cuda_error)";
     case TMX_ERR_UNSUPPORTED: return "request not supported by this build";
+    case TMX_ERR_STATIC_SCRATCH:
+      return "tmx_prefill_attn_static: the request needs more scratch than the 16 MiB static array "
+             "(TMX_STATIC_SCRATCH_BYTES); call tmx_prefill_attn with a caller-provided workspace";
     default: return "unknown status";
   }
 }
@@ -337,4 +340,58 @@ extern "C" int tmx_chunked_prefill_attn(void* out, const void* q, const int32_t*
   p.si = si; p.sl = sl; p.last = last; p.mode = mode;
   p.scale_log2 = scale_log2;
   return run_plan(pl, p, static_cast<uint8_t*>(workspace), (cudaStream_t)stream);
+}
+
+// ---- allocation-free variant of tmx_prefill_attn ----------------------------------------------------------
+// No counterpart in the reference (include/tmx.h).  The scratch the
+// attention kernels need (block index, split-KV partials) lives in this file-scope device array instead of a caller
+// workspace.  In host code `g_static_scratch` is only a stand-in for the symbol: its DEVICE address is taken once per
+// device with cudaGetSymbolAddress (that device current) and that pointer is what the kernels get.
+static __device__ __align__(256) unsigned char g_static_scratch[TMX_STATIC_SCRATCH_BYTES];
+
+namespace {
+constexpr int kScratchMaxDevices = 64;
+std::mutex g_scratch_mu;
+void* g_scratch_addr[kScratchMaxDevices] = {};
+
+int static_scratch_address(void** addr) {
+  int dev = -1;
+  TMX_CUDA_TRY(cudaGetDevice(&dev));
+  if (dev < 0 || dev >= kScratchMaxDevices) return TMX_ERR_UNSUPPORTED;
+  std::lock_guard<std::mutex> lk(g_scratch_mu);
+  if (g_scratch_addr[dev] == nullptr) {
+    void* ptr = nullptr;
+    TMX_CUDA_TRY(cudaGetSymbolAddress(&ptr, g_static_scratch));      // `dev` is the current device
+    if (ptr == nullptr) return TMX_ERR_CUDA;
+    g_scratch_addr[dev] = ptr;
+  }
+  *addr = g_scratch_addr[dev];
+  return TMX_OK;
+}
+}  // namespace
+
+extern "C" int tmx_prefill_attn_static(void* out, const void* q, const void* k, const void* v,
+                                       const int32_t* cu_seqlens, int B, int total_T, int max_seqlen,
+                                       int Hq, int Hkv, int D, int64_t q_stride_t, int64_t kv_stride_t,
+                                       int64_t o_stride_t, float scale, int si, int sl, int last,
+                                       int mode, const uint32_t* bitmask, int64_t bitmask_stride_words,
+                                       float* lse, int kernel, tmx_stream_t stream) {
+  reset_launch_count();
+  int st = check_common(B, total_T, max_seqlen, Hq, Hkv, D, q_stride_t, kv_stride_t, o_stride_t, mode, kernel);
+  if (st != TMX_OK) return st;
+  if (B == 0 || total_T == 0) return TMX_OK;
+  if (max_seqlen <= 0 || max_seqlen > total_T) return TMX_ERR_BAD_ARG;
+  // the same plan tmx_prefill_attn will make: its scratch must fit the static array
+  const bool scale_pos = scale * 1.4426950408889634f > 0.f;
+  const Plan pl = make_plan(B, total_T, max_seqlen, Hq, Hkv, si, sl, last, mode, kernel, bitmask != nullptr,
+                            scale_pos, false);
+  if (pl.total > (size_t)TMX_STATIC_SCRATCH_BYTES) return TMX_ERR_STATIC_SCRATCH;
+  st = check_arch();
+  if (st != TMX_OK) return st;
+  void* scratch = nullptr;
+  st = static_scratch_address(&scratch);
+  if (st != TMX_OK) return st;
+  return tmx_prefill_attn(out, q, k, v, cu_seqlens, B, total_T, max_seqlen, Hq, Hkv, D, q_stride_t, kv_stride_t,
+                          o_stride_t, scale, si, sl, last, mode, bitmask, bitmask_stride_words, lse, scratch,
+                          (size_t)TMX_STATIC_SCRATCH_BYTES, kernel, stream);
 }
