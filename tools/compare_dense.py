@@ -57,7 +57,7 @@ def main():
                 return None
 
         ours = torch.empty_like(q)
-        record("libtmx tcgen05 v3 (this repo)",
+        record("libtmx (this repo, kernel=auto: CTA-pair tcgen05 kernel)",
                lambda: ops.prefill_attn(q, k, v, cu, n, scale, 0, 0, 0, ops.DENSE_CAUSAL, out=ours))
 
         def fa2():
