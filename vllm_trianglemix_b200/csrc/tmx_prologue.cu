@@ -205,8 +205,12 @@ int launch(const PrologueParams& p, cudaStream_t s) {
   static void (*kernel)(const PrologueParams) = nullptr;
   static void (*copy_kernel)(const PrologueParams) = nullptr;
   if (ctas_per_sm == 0) {
+#ifdef TMX_DEV
     const char* e = std::getenv("TMX_PROLOGUE_VARIANT");   // developer switch: 1 = 4 CTAs/SM build (64 regs, small spill)
     const bool v1 = e && std::atoi(e) == 1;
+#else
+    const bool v1 = false;                                 // the product library reads no environment variable
+#endif
     kernel = v1 ? prologue_kernel<true, 4> : prologue_kernel<true, kMinCtasPerSm>;
     copy_kernel = prologue_kernel<false, kMinCtasPerSm>;
     TMX_CUDA_TRY(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&ctas_per_sm, kernel, kThreads, 0));
