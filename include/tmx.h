@@ -38,7 +38,7 @@ typedef struct CUstream_st* tmx_stream_t; /* == cudaStream_t */
 typedef enum {
   TMX_OK = 0,
   TMX_ERR_BAD_ARG = 1,      /* null pointer, negative size, unknown enum        */
-  TMX_ERR_BAD_SHAPE = 2,    /* head_dim != 128, Hq % Hkv != 0, ...              */
+  TMX_ERR_BAD_SHAPE = 2,    /* head_dim not 128 / 64, Hq % Hkv != 0, ...        */
   TMX_ERR_ALIGNMENT = 3,    /* pointer / stride not 16-byte aligned             */
   TMX_ERR_WORKSPACE = 4,    /* workspace null or smaller than tmx_attn_workspace_bytes */
   TMX_ERR_ARCH = 5,         /* device is not compute capability 10.x            */
@@ -134,7 +134,9 @@ int tmx_block_index(int32_t* ranges, int32_t* counts, int32_t* full,
  * get_attention_mask folded into tile skipping + an in-register predicate, in the
  * varlen layout of vLLM's AttentionImpl.forward
  * (vllm/attention/backends/abstract.py:158-171; q [T,Hq,D], k/v [T,Hkv,D]).
- * bf16 in, bf16 out, fp32 accumulation.  D must be 128.
+ * bf16 in, bf16 out, fp32 accumulation.  D must be 128 (Qwen3; every kernel) or 64 (the shape of the
+ * reference's own demo of this op, examples/trianglemix_quickstart.py:163-188; served by the mma.sync kernel:
+ * TMX_KERNEL_AUTO picks it, an explicit tcgen05 request returns TMX_ERR_UNSUPPORTED).
  * strides are in elements between consecutive tokens; heads are contiguous
  * (stride D).  cu_seqlens: int32 [B+1] device.  lse (optional): float [Hq, total_T],
  * natural-log-sum-exp of the scaled masked scores.

@@ -177,6 +177,6 @@ def test_forward_errors(tmx):
         op(q.to(DEV), k[:, :, :2].to(DEV), v[:, :, :2].to(DEV))            # GQA without num_kv_heads=
     with pytest.raises(tmx.TmxError, match="CUDA"):
         op(q, k, v)                                                         # CPU tensors: no CPU path
-    q64 = torch.randn(1, s, h, 64).bfloat16().to(DEV)
+    q32 = torch.randn(1, s, h, 32).bfloat16().to(DEV)
     with pytest.raises(tmx.TmxError, match="head_dim|shape"):
-        op(q64, q64, q64)                                                   # head_dim must be 128
+        op(q32, q32, q32)                                                   # head_dim must be 128 or 64

@@ -151,3 +151,22 @@ def test_middle_gate_gradient_closed_form_equals_autograd():
     g2 = (m * (1 - m) * ((o_m - o_t) * do.float().transpose(0, 1)).sum(-1)).transpose(0, 1)
     assert float((g - g2).abs().max()) < 1e-4
     assert float(g.abs().max()) > 1e-2
+
+
+# ---- head_dim 64 (the reference's own demo shape, tests/golden/make_golden_d64.py) ------------------------
+ATTN64 = np.load(os.path.join(GOLDEN, "attn_d64.npz"))
+
+
+def test_attention_d64_matches_reference():
+    """The oracle is head_dim-agnostic: the quickstart demo (no mask => bidirectional, B = 2) and two masked GQA
+    cases at D = 64 against outputs of the unmodified reference op."""
+    q, k, v = (_bf16(ATTN64["demo_" + n]) for n in "qkv")
+    out = orc.attention_fp32(q, k, v, None, 64 ** -0.5)
+    assert torch.allclose(out, torch.from_numpy(ATTN64["demo_out"]), atol=2e-6, rtol=1e-5)
+    for tag in ("t", "u"):
+        b, s, hq, hkv, d, si, sl, last = [int(x) for x in ATTN64[tag + "_params"]]
+        q, k, v = (_bf16(ATTN64["%s_%s" % (tag, n)]) for n in "qkv")
+        for name, mode in (("tri", orc.TRIANGLE), ("dense", orc.DENSE_CAUSAL)):
+            add = torch.from_numpy(orc.additive(orc.mask_closed(s, si, sl, last, mode)))
+            out = orc.attention_fp32(q, k, v, add, d ** -0.5)
+            assert torch.allclose(out, torch.from_numpy(ATTN64["%s_%s_out" % (tag, name)]), atol=2e-6, rtol=1e-5)

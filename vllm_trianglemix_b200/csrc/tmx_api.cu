@@ -112,10 +112,11 @@ struct Plan {
 //                             tail) + split-KV tail on tcgen05 while last - 1 <= kTailTcMaxRows
 // mma.sync serves odd GQA ratios, non-positive scales and explicit kernel="mma" (the cross-check).
 // `ctx`: the call carries context keys (chunked prefill / decode): block-index kernels only.
+// `D`: head_dim.  The tcgen05 kernels are built for 128 (Qwen3); 64 is served by the mma.sync kernel alone.
 Plan make_plan(int B, int total_T, int max_seqlen, int Hq, int Hkv, int si, int sl, int last, int mode,
-               int kernel, bool has_bitmask, bool scale_pos, bool ctx, bool paged = false) {
+               int kernel, bool has_bitmask, bool scale_pos, bool ctx, bool paged = false, int D = 128) {
   Plan pl{};
-  const bool pairable = Hkv > 0 && Hq % Hkv == 0 && (Hq / Hkv) % 2 == 0;
+  const bool pairable = D == 128 && Hkv > 0 && Hq % Hkv == 0 && (Hq / Hkv) % 2 == 0;
   pl.kernel = kernel;
   // explicit request for the CTA-pair kernel (AUTO's choice between the two tcgen05 kernels: see below)
   pl.pair = kernel == TMX_KERNEL_TCGEN05_PAIR;
@@ -203,7 +204,7 @@ extern "C" const char* tmx_strerror(int status) {
   switch (status) {
     case TMX_OK: return "ok";
     case TMX_ERR_BAD_ARG: return "bad argument (null pointer, negative size or unknown enum)";
-    case TMX_ERR_BAD_SHAPE: return "unsupported shape (head_dim must be 128, Hq % Hkv == 0, strides >= H*D)";
+    case TMX_ERR_BAD_SHAPE: return "unsupported shape (head_dim must be 128 or 64, Hq % Hkv == 0, strides >= H*D)";
     case TMX_ERR_ALIGNMENT: return "pointer or stride not 16-byte aligned";
     case TMX_ERR_WORKSPACE: return "workspace missing or smaller than tmx_attn_workspace_bytes()";
     case TMX_ERR_ARCH: return "device is not compute capability 10.x (B200, sm_100a)";
@@ -234,13 +235,12 @@ extern "C" void tmx_dev_set_trace(long long* buf) { g_trace = buf; }
 
 extern "C" size_t tmx_attn_workspace_bytes(int B, int total_T, int max_seqlen, int Hq, int Hkv,
                                            int D, int si, int sl, int last, int mode, int kernel) {
-  (void)D;
   if (B <= 0 || total_T <= 0) return 256;
   // a bitmask or the sign of the scale (unknown here) change the plan: size for the largest one
   size_t best = 0;
   for (int v = 0; v < 4; ++v) {
     const size_t t = make_plan(B, total_T, max_seqlen, Hq, Hkv, si, sl, last, mode, kernel, (v & 1) != 0,
-                               (v & 2) != 0, false).total;
+                               (v & 2) != 0, false, false, D).total;
     best = t > best ? t : best;
   }
   return best;
@@ -252,7 +252,8 @@ int check_common(int B, int total_T, int max_seqlen, int Hq, int Hkv, int D, int
   if (B < 0 || total_T < 0 || max_seqlen < 0 || Hq <= 0 || Hkv <= 0) return TMX_ERR_BAD_ARG;
   if (mode < TMX_MODE_DENSE_CAUSAL || mode > TMX_MODE_NONE) return TMX_ERR_BAD_ARG;
   if (kernel < TMX_KERNEL_AUTO || kernel > TMX_KERNEL_TCGEN05_PAIR) return TMX_ERR_BAD_ARG;
-  if (D != 128 || Hq % Hkv != 0) return TMX_ERR_BAD_SHAPE;
+  if ((D != 128 && D != 64) || Hq % Hkv != 0) return TMX_ERR_BAD_SHAPE;
+  if (D != 128 && kernel >= TMX_KERNEL_TCGEN05) return TMX_ERR_UNSUPPORTED;   // tcgen05 kernels: head_dim 128 only
   if (q_stride_t < (int64_t)Hq * D || kv_stride_t < (int64_t)Hkv * D || o_stride_t < (int64_t)Hq * D)
     return TMX_ERR_BAD_SHAPE;
   return TMX_OK;
@@ -285,7 +286,7 @@ extern "C" int tmx_prefill_attn(void* out, const void* q, const void* k, const v
   // an explicit tcgen05 request cannot be served with a non-positive scale; AUTO falls back to mma.sync
   if (kernel >= TMX_KERNEL_TCGEN05 && !scale_pos) return TMX_ERR_UNSUPPORTED;
   Plan pl = make_plan(B, total_T, max_seqlen, Hq, Hkv, si, sl, last, mode, kernel, bitmask != nullptr,
-                      scale_pos, false);
+                      scale_pos, false, false, D);
   if (!workspace || workspace_bytes < pl.total || misaligned(workspace)) return TMX_ERR_WORKSPACE;
 
   AttnParams p{};
@@ -293,7 +294,7 @@ extern "C" int tmx_prefill_attn(void* out, const void* q, const void* k, const v
   p.out = (__nv_bfloat16*)out; p.lse = lse; p.cu = cu_seqlens;
   p.bitmask = bitmask; p.bitmask_stride = bitmask_stride_words;
   p.q_stride = q_stride_t; p.kv_stride = kv_stride_t; p.o_stride = o_stride_t;
-  p.B = B; p.total_T = total_T; p.total_kv = total_T; p.max_seqlen = max_seqlen; p.Hq = Hq; p.Hkv = Hkv;
+  p.B = B; p.total_T = total_T; p.total_kv = total_T; p.max_seqlen = max_seqlen; p.Hq = Hq; p.Hkv = Hkv; p.D = D;
   p.si = si; p.sl = sl; p.last = last; p.mode = mode;
   p.scale_log2 = scale_log2;
   return run_plan(pl, p, static_cast<uint8_t*>(workspace), (cudaStream_t)stream);
@@ -327,7 +328,7 @@ extern "C" int tmx_chunked_prefill_attn(void* out, const void* q, const int32_t*
   const bool scale_pos = scale_log2 > 0.f;
   if (kernel >= TMX_KERNEL_TCGEN05 && !scale_pos) return TMX_ERR_UNSUPPORTED;
   Plan pl = make_plan(B, total_Tq, max_query_len, Hq, Hkv, si, sl, last, mode, kernel, false, scale_pos, true,
-                      block_table != nullptr);
+                      block_table != nullptr, D);
   if (!workspace || workspace_bytes < pl.total || misaligned(workspace)) return TMX_ERR_WORKSPACE;
 
   AttnParams p{};
@@ -336,7 +337,7 @@ extern "C" int tmx_chunked_prefill_attn(void* out, const void* q, const int32_t*
   p.kv_lens = seq_lens; p.cu_k = cu_seqlens_k; p.block_table = block_table;
   p.bt_stride = block_table_stride; p.page_size = page_size;
   p.q_stride = q_stride_t; p.kv_stride = kv_stride_t; p.o_stride = o_stride_t;
-  p.B = B; p.total_T = total_Tq; p.total_kv = kv_rows; p.max_seqlen = max_query_len; p.Hq = Hq; p.Hkv = Hkv;
+  p.B = B; p.total_T = total_Tq; p.total_kv = kv_rows; p.max_seqlen = max_query_len; p.Hq = Hq; p.Hkv = Hkv; p.D = D;
   p.si = si; p.sl = sl; p.last = last; p.mode = mode;
   p.scale_log2 = scale_log2;
   return run_plan(pl, p, static_cast<uint8_t*>(workspace), (cudaStream_t)stream);
@@ -384,7 +385,7 @@ extern "C" int tmx_prefill_attn_static(void* out, const void* q, const void* k, 
   // the same plan tmx_prefill_attn will make: its scratch must fit the static array
   const bool scale_pos = scale * 1.4426950408889634f > 0.f;
   const Plan pl = make_plan(B, total_T, max_seqlen, Hq, Hkv, si, sl, last, mode, kernel, bitmask != nullptr,
-                            scale_pos, false);
+                            scale_pos, false, false, D);
   if (pl.total > (size_t)TMX_STATIC_SCRATCH_BYTES) return TMX_ERR_STATIC_SCRATCH;
   st = check_arch();
   if (st != TMX_OK) return st;

@@ -26,6 +26,7 @@ struct AttnParams {
   float2* part_ml;
   long long q_stride, kv_stride, o_stride;   // elements per token (paged: per cache slot)
   int B, total_T, max_seqlen, Hq, Hkv;
+  int D;                      // head_dim: 128 (every kernel) or 64 (mma.sync kernel only)
   long long total_kv;         // rows of the K/V buffer (contiguous: tokens; paged: num_blocks * page_size)
   int n_slots, last_tiles, nsplit_max;
   int si, sl, last, mode;

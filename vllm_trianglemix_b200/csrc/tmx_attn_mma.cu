@@ -16,9 +16,9 @@
 namespace tmx {
 namespace {
 
-constexpr int kD = 128;
 constexpr int kBN = 64;
-constexpr int kTileBytes = kBN * kD * 2;  // 16 KB
+// head_dim kD is a template parameter of the kernels: 128 (Qwen3) or 64 (the shape of the reference's own
+// demo of this op, examples/trianglemix_quickstart.py:163-188; served by this kernel only).
 
 __device__ __forceinline__ uint32_t smem_u32(const void* p) {
   return (uint32_t)__cvta_generic_to_shared(p);
@@ -53,27 +53,33 @@ __device__ __forceinline__ uint32_t pack_bf16(float lo, float hi) {
   __nv_bfloat162 v = __floats2bfloat162_rn(lo, hi);
   return *reinterpret_cast<uint32_t*>(&v);
 }
-// byte offset of 16-byte chunk `chunk` of row `row` in a [rows][128] bf16 tile, XOR-swizzled
+// byte offset of 16-byte chunk `chunk` of row `row` in a [rows][kD] bf16 tile, XOR-swizzled
+// (kD / 8 = 16 or 8 chunks per row: the XOR with row & 7 stays inside the row either way)
+template <int kD>
 __device__ __forceinline__ uint32_t swz(int row, int chunk) {
-  return (uint32_t)(row * 256 + ((chunk ^ (row & 7)) << 4));
+  return (uint32_t)(row * (kD * 2) + ((chunk ^ (row & 7)) << 4));
 }
 
-// Load `rows` rows x 128 bf16 from global (row stride `stride` elements) into a swizzled tile.
+// Load `rows` rows x kD bf16 from global (row stride `stride` elements) into a swizzled tile.
 // Rows with index >= valid_rows are zero-filled.
-template <int kThreads>
+template <int kThreads, int kD>
 __device__ __forceinline__ void load_tile(uint32_t sdst, const __nv_bfloat16* g, long long stride,
                                           int rows, int valid_rows, int tid) {
-  for (int c = tid; c < rows * 16; c += kThreads) {
-    int r = c >> 4, ch = c & 15;
+  constexpr int kChunks = kD / 8;
+  for (int c = tid; c < rows * kChunks; c += kThreads) {
+    int r = c / kChunks, ch = c % kChunks;
     bool ok = r < valid_rows;
     const __nv_bfloat16* src = g + (long long)(ok ? r : 0) * stride + ch * 8;
-    cp_async16(sdst + swz(r, ch), src, ok);
+    cp_async16(sdst + swz<kD>(r, ch), src, ok);
   }
 }
 
-template <int BM>
+template <int BM, int kD>
 __global__ void __launch_bounds__(BM * 2, (BM == 64 ? 3 : 1)) attn_mma_kernel(const AttnParams p) {
   constexpr int kThreads = BM * 2;
+  constexpr int kTileBytes = kBN * kD * 2;  // 16 KB (kD = 128) / 8 KB (kD = 64)
+  constexpr int kChunks = kD / 8;           // 16-byte chunks per row
+  constexpr int kKSteps = kD / 16;          // k-steps of the score MMA = 16-column pairs of the output
   extern __shared__ __align__(128) uint8_t smem[];
   // layout: K stage0 | K stage1 | V stage0 | V stage1 ; Q is staged through the V region first
   const uint32_t sK = smem_u32(smem);
@@ -140,15 +146,15 @@ __global__ void __launch_bounds__(BM * 2, (BM == 64 ? 3 : 1)) attn_mma_kernel(co
   auto load_kv_tile = [&](uint32_t sdst, const __nv_bfloat16* base, int tile) {
     const int valid = min(kBN, n - tile * kBN);
     if (pages == nullptr) {
-      load_tile<kThreads>(sdst, base + (long long)tile * kBN * p.kv_stride, p.kv_stride, kBN, valid, tid);
+      load_tile<kThreads, kD>(sdst, base + (long long)tile * kBN * p.kv_stride, p.kv_stride, kBN, valid, tid);
       return;
     }
-    for (int c = tid; c < kBN * 16; c += kThreads) {
-      const int r = c >> 4, ch = c & 15;
+    for (int c = tid; c < kBN * kChunks; c += kThreads) {
+      const int r = c / kChunks, ch = c % kChunks;
       const bool ok = r < valid;
       const int key = tile * kBN + (ok ? r : 0);
       const long long slot = (long long)pages[key / p.page_size] * p.page_size + key % p.page_size;
-      cp_async16(sdst + swz(r, ch), base + slot * p.kv_stride + ch * 8, ok);
+      cp_async16(sdst + swz<kD>(r, ch), base + slot * p.kv_stride + ch * 8, ok);
     }
   };
   auto issue_kv = [&](int it) {
@@ -158,25 +164,25 @@ __global__ void __launch_bounds__(BM * 2, (BM == 64 ? 3 : 1)) attn_mma_kernel(co
   };
 
   // ---- prologue: Q through the V region, K tile 0 alongside ------------------
-  load_tile<kThreads>(sV, qg, p.q_stride, BM, r1 - r0 + 1, tid);
+  load_tile<kThreads, kD>(sV, qg, p.q_stride, BM, r1 - r0 + 1, tid);
   load_kv_tile(sK, kg, tile_of(0));
   cp_async_commit();
   cp_async_wait<0>();
   __syncthreads();
-  uint32_t qa[8][4];
+  uint32_t qa[kKSteps][4];
   {
     int row = warp * 16 + (lane & 15);
 #pragma unroll
-    for (int ks = 0; ks < 8; ++ks)
-      ldsm_x4(sV + swz(row, 2 * ks + (lane >> 4)), qa[ks][0], qa[ks][1], qa[ks][2], qa[ks][3]);
+    for (int ks = 0; ks < kKSteps; ++ks)
+      ldsm_x4(sV + swz<kD>(row, 2 * ks + (lane >> 4)), qa[ks][0], qa[ks][1], qa[ks][2], qa[ks][3]);
   }
   __syncthreads();
   load_kv_tile(sV, vg, tile_of(0));
   cp_async_commit();
 
-  float o[16][4];
+  float o[kChunks][4];
 #pragma unroll
-  for (int i = 0; i < 16; ++i) o[i][0] = o[i][1] = o[i][2] = o[i][3] = 0.f;
+  for (int i = 0; i < kChunks; ++i) o[i][0] = o[i][1] = o[i][2] = o[i][3] = 0.f;
   float m_run[2] = {-INFINITY, -INFINITY}, l_run[2] = {0.f, 0.f};
   const float sc = p.scale_log2;
   const int row_a = r0 + warp * 16 + g, row_b = row_a + 8;   // rows inside the sequence
@@ -197,13 +203,13 @@ __global__ void __launch_bounds__(BM * 2, (BM == 64 ? 3 : 1)) attn_mma_kernel(co
 #pragma unroll
     for (int i = 0; i < 8; ++i) s[i][0] = s[i][1] = s[i][2] = s[i][3] = 0.f;
 #pragma unroll
-    for (int ks = 0; ks < 8; ++ks) {
+    for (int ks = 0; ks < kKSteps; ++ks) {
 #pragma unroll
       for (int np = 0; np < 4; ++np) {
         int key = np * 16 + ((lane >> 4) << 3) + (lane & 7);
         int chunk = 2 * ks + ((lane >> 3) & 1);
         uint32_t b0, b1, b2, b3;
-        ldsm_x4(kbase + swz(key, chunk), b0, b1, b2, b3);
+        ldsm_x4(kbase + swz<kD>(key, chunk), b0, b1, b2, b3);
         mma_bf16(s[2 * np], qa[ks], b0, b1);
         mma_bf16(s[2 * np + 1], qa[ks], b2, b3);
       }
@@ -273,7 +279,7 @@ __global__ void __launch_bounds__(BM * 2, (BM == 64 ? 3 : 1)) attn_mma_kernel(co
     l_run[0] = l_run[0] * alpha[0] + rs[0];
     l_run[1] = l_run[1] * alpha[1] + rs[1];
 #pragma unroll
-    for (int i = 0; i < 16; ++i) {
+    for (int i = 0; i < kChunks; ++i) {
       o[i][0] *= alpha[0]; o[i][1] *= alpha[0]; o[i][2] *= alpha[1]; o[i][3] *= alpha[1];
     }
 
@@ -286,11 +292,11 @@ __global__ void __launch_bounds__(BM * 2, (BM == 64 ? 3 : 1)) attn_mma_kernel(co
       pa[2] = pack_bf16(s[2 * kk + 1][0], s[2 * kk + 1][1]);
       pa[3] = pack_bf16(s[2 * kk + 1][2], s[2 * kk + 1][3]);
 #pragma unroll
-      for (int dp = 0; dp < 8; ++dp) {
+      for (int dp = 0; dp < kKSteps; ++dp) {
         int key = kk * 16 + (((lane >> 3) & 1) << 3) + (lane & 7);
         int chunk = 2 * dp + (lane >> 4);
         uint32_t b0, b1, b2, b3;
-        ldsm_x4_t(vbase + swz(key, chunk), b0, b1, b2, b3);
+        ldsm_x4_t(vbase + swz<kD>(key, chunk), b0, b1, b2, b3);
         mma_bf16(o[2 * dp], pa, b0, b1);
         mma_bf16(o[2 * dp + 1], pa, b2, b3);
       }
@@ -311,7 +317,7 @@ __global__ void __launch_bounds__(BM * 2, (BM == 64 ? 3 : 1)) attn_mma_kernel(co
     float2* pml = p.part_ml + ((long long)part * p.Hq + head) * BM;
     int ra = warp * 16 + g, rb = ra + 8;
 #pragma unroll
-    for (int i = 0; i < 16; ++i) {
+    for (int i = 0; i < kChunks; ++i) {
       *reinterpret_cast<float2*>(po + ra * kD + i * 8 + t4 * 2) = make_float2(o[i][0], o[i][1]);
       *reinterpret_cast<float2*>(po + rb * kD + i * 8 + t4 * 2) = make_float2(o[i][2], o[i][3]);
     }
@@ -326,22 +332,22 @@ __global__ void __launch_bounds__(BM * 2, (BM == 64 ? 3 : 1)) attn_mma_kernel(co
   {
     int ra = warp * 16 + g, rb = ra + 8;
 #pragma unroll
-    for (int i = 0; i < 16; ++i) {
+    for (int i = 0; i < kChunks; ++i) {
       uint32_t va = pack_bf16(o[i][0] * inv[0], o[i][1] * inv[0]);
       uint32_t vb = pack_bf16(o[i][2] * inv[1], o[i][3] * inv[1]);
-      asm volatile("st.shared.b32 [%0], %1;\n" ::"r"(sK + swz(ra, i) + t4 * 4), "r"(va));
-      asm volatile("st.shared.b32 [%0], %1;\n" ::"r"(sK + swz(rb, i) + t4 * 4), "r"(vb));
+      asm volatile("st.shared.b32 [%0], %1;\n" ::"r"(sK + swz<kD>(ra, i) + t4 * 4), "r"(va));
+      asm volatile("st.shared.b32 [%0], %1;\n" ::"r"(sK + swz<kD>(rb, i) + t4 * 4), "r"(vb));
     }
   }
   __syncthreads();
   __nv_bfloat16* og = p.out + (long long)(seq_start + r0) * p.o_stride + head * kD;
   const int valid = r1 - r0 + 1;
-  for (int c = tid; c < BM * 16; c += kThreads) {
-    int r = c >> 4, ch = c & 15;
+  for (int c = tid; c < BM * kChunks; c += kThreads) {
+    int r = c / kChunks, ch = c % kChunks;
     if (r < valid) {
       uint4 v;
       asm volatile("ld.shared.v4.b32 {%0,%1,%2,%3}, [%4];\n"
-                   : "=r"(v.x), "=r"(v.y), "=r"(v.z), "=r"(v.w) : "r"(sK + swz(r, ch)));
+                   : "=r"(v.x), "=r"(v.y), "=r"(v.z), "=r"(v.w) : "r"(sK + swz<kD>(r, ch)));
       *reinterpret_cast<uint4*>(og + (long long)r * p.o_stride + ch * 8) = v;
     }
   }
@@ -356,7 +362,7 @@ __global__ void __launch_bounds__(BM * 2, (BM == 64 ? 3 : 1)) attn_mma_kernel(co
 // Merge the split-KV partials of one (sequence, last tile, head): a CTA takes 8 rows, one thread
 // per (row, 4 columns); grid.x = B * last_tiles * BM / 8 so that the merge is a bandwidth-bound
 // pass over the partials instead of 64 serial CTAs.
-template <int BM>
+template <int BM, int kD>
 __global__ void __launch_bounds__(256) combine_kernel(const AttnParams p) {
   constexpr int kRowsPerCta = 8;
   int e = blockIdx.x / (BM / kRowsPerCta);
@@ -374,7 +380,7 @@ __global__ void __launch_bounds__(256) combine_kernel(const AttnParams p) {
   if (ns == 0) return;
   long long base = (long long)(seq * p.last_tiles + ql) * p.nsplit_max;
   const int r = rblk * kRowsPerCta + (threadIdx.x >> 5), c4 = (threadIdx.x & 31) * 4;
-  if (r0 + r > r1) return;
+  if (r0 + r > r1 || c4 >= kD) return;     // kD = 64: the upper half-warp has no columns
   float mmax = -INFINITY;
   for (int s = 0; s < ns; ++s)
     mmax = fmaxf(mmax, p.part_ml[((base + s) * p.Hq + head) * BM + r].x);
@@ -398,18 +404,19 @@ __global__ void __launch_bounds__(256) combine_kernel(const AttnParams p) {
 
 }  // namespace
 
-template <int BM>
+template <int BM, int kD>
 int launch_attn_mma_t(const AttnParams& p, cudaStream_t s) {
-  constexpr int smem = 4 * kTileBytes;
-  TMX_SET_SMEM_ATTR(attn_mma_kernel<BM>, BM == 64 ? kAttrMma64 : kAttrMma128, smem);
+  constexpr int smem = 4 * kBN * kD * 2;        // K and V, two stages each: 64 KB (kD = 128) / 32 KB (kD = 64)
+  if constexpr (smem > 48 * 1024)               // (kD = 64 stays under the 48 KB every kernel may use)
+    TMX_SET_SMEM_ATTR((attn_mma_kernel<BM, kD>), BM == 64 ? kAttrMma64 : kAttrMma128, smem);
   int extra = (p.last_tiles > 0 && p.nsplit_max > 0) ? p.B * p.last_tiles * p.nsplit_max : 0;
   dim3 grid((unsigned)(p.n_slots + extra), (unsigned)p.Hq);
-  attn_mma_kernel<BM><<<grid, BM * 2, smem, s>>>(p);
+  attn_mma_kernel<BM, kD><<<grid, BM * 2, smem, s>>>(p);
   count_launch();
   TMX_CUDA_TRY(cudaGetLastError());
   if (extra > 0) {
     dim3 cg((unsigned)(p.B * p.last_tiles * (BM / 8)), (unsigned)p.Hq);
-    combine_kernel<BM><<<cg, 256, 0, s>>>(p);
+    combine_kernel<BM, kD><<<cg, 256, 0, s>>>(p);
     count_launch();
     TMX_CUDA_TRY(cudaGetLastError());
   }
@@ -417,7 +424,8 @@ int launch_attn_mma_t(const AttnParams& p, cudaStream_t s) {
 }
 
 int launch_attn_mma(const AttnParams& p, int bm, cudaStream_t s) {
-  return bm == 64 ? launch_attn_mma_t<64>(p, s) : launch_attn_mma_t<128>(p, s);
+  if (p.D == 64) return bm == 64 ? launch_attn_mma_t<64, 64>(p, s) : launch_attn_mma_t<128, 64>(p, s);
+  return bm == 64 ? launch_attn_mma_t<64, 128>(p, s) : launch_attn_mma_t<128, 128>(p, s);
 }
 
 }  // namespace tmx
